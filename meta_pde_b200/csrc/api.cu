@@ -1,0 +1,658 @@
+// api.cu -- the C ABI of libmetapde_b200 (include/metapde_b200.h): argument validation,
+// workspace carving, launch planning, and the stream-ordered MAML / LEAP rollouts.
+// No allocation, no synchronisation, no mutable global state besides one-time
+// kernel attributes and a launch counter.
+#include "../../include/metapde_b200.h"
+#include "host_common.h"
+#include "aux_kernels.cuh"
+#include <mutex>
+
+namespace mpde {
+
+std::atomic<long long> g_launches{0};
+
+int device_sm_count() {
+#ifdef MPDE_EMU
+  return 4;
+#else
+  static int n = 0;
+  static std::once_flag once;
+  std::call_once(once, []() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n < 1) n = 148;
+  });
+  return n;
+#endif
+}
+
+static int dispatch(int W, int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  switch (W) {
+    case 32: return dispatch_w32(pde, mode, op, p, gx, gy, stream, info);
+    case 64: return dispatch_w64(pde, mode, op, p, gx, gy, stream, info);
+    case 128: return dispatch_w128(pde, mode, op, p, gx, gy, stream, info);
+    case 256: return dispatch_w256(pde, mode, op, p, gx, gy, stream, info);
+  }
+  return MPDE_UNSUPPORTED_NET;
+}
+
+static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+struct Carver {
+  char* base; size_t off, cap;
+  Carver(void* b, size_t c) : base((char*)b), off(0), cap(c) {}
+  float* take(size_t nfloats) {
+    size_t bytes = align_up(nfloats * sizeof(float));
+    float* p = (float*)(base ? base + off : nullptr);
+    off += bytes;
+    return p;
+  }
+  bool ok() const { return off <= cap; }
+};
+
+static int pde_out_dim(int kind) { return kind == MPDE_PDE_HYPER_ELASTICITY ? 2 : 1; }
+
+static int check_net(const mpde_net_desc* net, int out_dim_required) {
+  if (!net) return MPDE_INVALID_ARG;
+  if (net->num_layers < 1 || net->num_layers > 32) return MPDE_UNSUPPORTED_NET;
+  if (net->in_dim != 2) return MPDE_UNSUPPORTED_NET;
+  if (net->layer_size != 32 && net->layer_size != 64 && net->layer_size != 128 && net->layer_size != 256)
+    return MPDE_UNSUPPORTED_NET;
+  if (net->out_dim != 1 && net->out_dim != 2) return MPDE_UNSUPPORTED_NET;
+  if (out_dim_required && net->out_dim != out_dim_required) return MPDE_UNSUPPORTED_NET;
+  return MPDE_OK;
+}
+
+// -------------------------------------------------------------------------
+// evaluation plan: segments, tiles, CTAs per task, workspace
+// -------------------------------------------------------------------------
+struct EvalPlan {
+  int W, L, OUT, P, PH, pde, mode, T;
+  int n_seg;
+  int head[MAX_SEG], npts[MAX_SEG], term_of_seg[MAX_SEG];
+  float term_scale[MAX_SEG], weight[MAX_SEG], inv_elems[MAX_SEG];
+  int tile_begin[MAX_SEG + 1];
+  int n_terms, domain_seg;
+  int G;                    // CTAs per task
+  KernelInfo ki;
+  size_t scratch_per_cta;   // floats
+  // workspace sizes (floats)
+  size_t n_th, n_thd, n_scratch, n_pg, n_ph, n_pt, n_gtmp;
+  size_t bytes;
+};
+
+static int kernel_pde(int kind) { return kind == MPDE_PDE_POISSON ? PDE_POISSON : kind == MPDE_PDE_TD_BURGERS ? PDE_BURGERS : PDE_HYPER; }
+
+static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, int mode, bool need_gtmp, EvalPlan* pl) {
+  if (!pde || T < 1) return MPDE_INVALID_ARG;
+  if (pde->kind < 0 || pde->kind > 2) return MPDE_INVALID_ARG;
+  if (mode < 0 || mode > 2) return MPDE_INVALID_ARG;
+  int rc = check_net(net, pde_out_dim(pde->kind));
+  if (rc) return rc;
+  pl->W = net->layer_size; pl->L = net->num_layers; pl->OUT = net->out_dim;
+  pl->P = mpde_param_count(net);
+  pl->PH = ph_count(pl->W, pl->L, pl->OUT);
+  pl->pde = kernel_pde(pde->kind); pl->mode = mode; pl->T = T;
+  const float bw = pde->bc_weight;
+  if (pde->kind == MPDE_PDE_POISSON) {
+    pl->n_seg = 2; pl->n_terms = 2; pl->domain_seg = 1;
+    const int heads[2] = {HEAD_POISSON_BOUNDARY, HEAD_POISSON_DOMAIN};
+    for (int s = 0; s < 2; ++s) { pl->head[s] = heads[s]; pl->term_of_seg[s] = s; pl->term_scale[s] = 1.f; }
+    pl->weight[0] = bw; pl->weight[1] = 1.f;
+  } else if (pde->kind == MPDE_PDE_TD_BURGERS) {
+    pl->n_seg = 4; pl->n_terms = 4; pl->domain_seg = 3;
+    const int heads[4] = {HEAD_BURGERS_IC, HEAD_BURGERS_IC, HEAD_BURGERS_IC, HEAD_BURGERS_DOMAIN};
+    const int terms[4] = {1, 2, 0, 3};   // sets: left, right, initial, domain -> terms: initial, left, right, domain
+    for (int s = 0; s < 4; ++s) { pl->head[s] = heads[s]; pl->term_of_seg[s] = terms[s]; pl->term_scale[s] = 1.f; pl->weight[s] = (s < 3) ? bw : 1.f; }
+  } else {
+    pl->n_seg = 3; pl->n_terms = 3; pl->domain_seg = 2;
+    const int heads[3] = {HEAD_HYPER_TOP, HEAD_HYPER_BOTTOM, HEAD_HYPER_DOMAIN};
+    const int terms[3] = {1, 0, 2};      // sets: top, bottom, domain -> terms: bottom, top, domain
+    for (int s = 0; s < 3; ++s) { pl->head[s] = heads[s]; pl->term_of_seg[s] = terms[s]; }
+    pl->term_scale[0] = 1000.f; pl->term_scale[1] = 1000.f; pl->term_scale[2] = 1.f;
+    pl->weight[0] = bw; pl->weight[1] = bw; pl->weight[2] = 1.f;
+  }
+  rc = dispatch(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
+  if (rc) return rc;
+  const int NP = pl->ki.np;
+  pl->tile_begin[0] = 0;
+  for (int s = 0; s < pl->n_seg; ++s) {
+    const int n = pde->n_points[s];
+    if (n < 1) return MPDE_INVALID_ARG;
+    pl->npts[s] = n;
+    const bool domain = (s == pl->domain_seg);
+    const int per_tile = domain ? NP : 4 * NP;
+    pl->tile_begin[s + 1] = pl->tile_begin[s] + (n + per_tile - 1) / per_tile;
+    const float elems = domain ? (float)n : (float)n * (float)pl->OUT;   // np.mean over [N] or [N, out_dim]
+    pl->inv_elems[s] = 1.f / elems;
+  }
+  // CTAs per task: minimise waves * tiles-per-CTA; prefer fewer CTAs on ties (fewer partial buffers)
+  const int tiles = pl->tile_begin[pl->n_seg];
+  const long long slots = (long long)device_sm_count() * pl->ki.occ;
+  int best_g = 1; double best_cost = 1e300;
+  const int gmax = tiles < 512 ? tiles : 512;
+  for (int g = 1; g <= gmax; ++g) {
+    const long long ctas = (long long)T * g;
+    const long long waves = (ctas + slots - 1) / slots;
+    const int per = (tiles + g - 1) / g;
+    const double cost = (double)waves * ((double)per + 0.15);   // 0.15 tile-equivalents of per-CTA overhead
+    if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_g = g; }
+  }
+  pl->G = best_g;
+  const size_t ctas = (size_t)T * pl->G;
+  const int nft_val = (mode == MODE_HVP) ? 3 : 2, nft_ch = (mode == MODE_HVP) ? 9 : 5;
+  const size_t per_layer = (size_t)pl->W * NP * (size_t)((4 * nft_val > nft_ch) ? 4 * nft_val : nft_ch);
+  pl->scratch_per_cta = (mode == MODE_LOSS) ? 0 : per_layer * pl->L;
+  pl->n_th = (size_t)T * pl->PH;
+  pl->n_thd = (mode == MODE_HVP) ? (size_t)T * pl->PH : 0;
+  pl->n_scratch = ctas * pl->scratch_per_cta;
+  pl->n_pg = (mode == MODE_LOSS) ? 0 : ctas * pl->P;
+  pl->n_ph = (mode == MODE_HVP) ? ctas * pl->P : 0;
+  pl->n_pt = ctas * MAX_SEG;
+  pl->n_gtmp = need_gtmp ? (size_t)T * pl->P : 0;
+  Carver c(nullptr, 0);
+  c.take(pl->n_th); c.take(pl->n_thd); c.take(pl->n_scratch); c.take(pl->n_pg); c.take(pl->n_ph); c.take(pl->n_pt); c.take(pl->n_gtmp);
+  pl->bytes = c.off + 256;
+  return MPDE_OK;
+}
+
+template <typename K, typename... Args>
+static int launch_simple(K kfn, int gx, int gy, int nt, size_t smem, void* stream, Args... args) {
+  MPDE_LAUNCH(kfn, dim3(gx, gy, 1), dim3(nt, 1, 1), smem, stream, args...);
+  return MPDE_CHECK_LAUNCH() ? MPDE_CUDA_ERROR : MPDE_OK;
+}
+
+static int grid_for(long long n, int nt = 256) {
+  long long g = (n + nt - 1) / nt;
+  const long long cap = (long long)device_sm_count() * 8;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+// One evaluation of loss / loss+grad / loss+grad+Hv for T tasks.
+static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, int mode, const float* theta,
+                    long long theta_stride, const float* v, long long v_stride, const mpde_points* points,
+                    const float* pde_params, float* loss, long long loss_stride, float* terms, long long terms_stride,
+                    float* domain_residual, float* grad, float* hv, int want_grad, void* workspace, size_t ws_bytes,
+                    void* stream) {
+  if (!net || !pde || !theta || !points || !pde_params) return MPDE_INVALID_ARG;
+  if (mode == MODE_GRAD && !grad) return MPDE_INVALID_ARG;
+  if (mode == MODE_HVP && (!hv || !v)) return MPDE_INVALID_ARG;
+  EvalPlan pl;
+  const bool need_gtmp = (mode == MODE_HVP) && !grad;
+  int rc = make_plan(net, pde, T, mode, need_gtmp, &pl);
+  if (rc) return rc;
+  if (!workspace || ws_bytes < pl.bytes) return MPDE_WORKSPACE_TOO_SMALL;
+  for (int s = 0; s < pl.n_seg; ++s) if (!points->set[s]) return MPDE_INVALID_ARG;
+  char* wsb = (char*)workspace;
+  wsb += (256 - ((uintptr_t)wsb & 255)) & 255;
+  Carver c(wsb, ws_bytes);
+  float* th = c.take(pl.n_th); float* thd = c.take(pl.n_thd); float* scratch = c.take(pl.n_scratch);
+  float* pg = c.take(pl.n_pg); float* ph = c.take(pl.n_ph); float* pt = c.take(pl.n_pt); float* gtmp = c.take(pl.n_gtmp);
+  if (mode != MODE_HVP) thd = nullptr;
+
+  // 1. prep: theta -> theta-hat (shared theta: prepared once)
+  const int T_prep = (theta_stride == 0 && (mode != MODE_HVP || v_stride == 0)) ? 1 : T;
+  {
+    PrepParams pp;
+    pp.W = pl.W; pp.L = pl.L; pp.OUT = pl.OUT; pp.log_scale = net->log_scale; pp.P = pl.P; pp.PH = pl.PH; pp.T = T_prep;
+    pp.theta = theta; pp.theta_stride = theta_stride;
+    pp.v = (mode == MODE_HVP) ? v : nullptr; pp.v_stride = v_stride;
+    pp.th = th; pp.thd = thd;
+    int gx = grid_for(pl.PH);
+    if (gx > 64) gx = 64;
+    rc = launch_simple(prep_kernel, gx, T_prep, 256, 0, stream, pp);
+    if (rc) return rc;
+  }
+  // 2. the fused jet kernel
+  KParams kp;
+  kp.L = pl.L; kp.P = pl.P; kp.PH = pl.PH; kp.omega = net->omega; kp.T = T; kp.n_seg = pl.n_seg;
+  for (int s = 0; s < pl.n_seg; ++s) {
+    kp.seg[s].pts = points->set[s];
+    kp.seg[s].task_stride = points->task_stride[s];
+    kp.seg[s].n = pl.npts[s];
+    kp.seg[s].head = pl.head[s];
+    kp.seg[s].coef = pl.weight[s] * pl.term_scale[s] * pl.inv_elems[s];
+    kp.seg[s].res_out = (s == pl.domain_seg && mode == MODE_LOSS) ? domain_residual : nullptr;
+    kp.seg[s].res_stride = pl.npts[s];
+  }
+  for (int s = 0; s <= pl.n_seg; ++s) kp.seg_tile_begin[s] = pl.tile_begin[s];
+  kp.prm = pde_params; kp.nprm = mpde_num_pde_params(pde->kind);
+  kp.th = th; kp.th_stride = (T_prep == 1) ? 0 : pl.PH;
+  kp.thd = thd; kp.thd_stride = (T_prep == 1) ? 0 : pl.PH;
+  kp.scratch = scratch; kp.scratch_per_cta = (long long)pl.scratch_per_cta;
+  kp.partial_g = pg; kp.partial_h = ph; kp.partial_terms = pt;
+  kp.want_grad = want_grad;
+  rc = dispatch(pl.W, pl.pde, mode, 1, &kp, pl.G, T, stream, nullptr);
+  if (rc) return rc;
+  // 3. loss terms
+  {
+    LossFinParams lp;
+    lp.G = pl.G; lp.n_seg = pl.n_seg; lp.n_terms = pl.n_terms;
+    for (int s = 0; s < pl.n_seg; ++s) {
+      lp.term_of_seg[s] = pl.term_of_seg[s]; lp.term_scale[s] = pl.term_scale[s];
+      lp.inv_elems[s] = pl.inv_elems[s]; lp.weight[s] = pl.weight[s];
+    }
+    lp.partial_terms = pt; lp.loss = loss; lp.terms = terms; lp.loss_stride = loss_stride; lp.terms_stride = terms_stride;
+    if (loss || terms) {
+      rc = launch_simple(loss_finalize_kernel, (T + 127) / 128, 1, 128, 0, stream, lp, T);
+      if (rc) return rc;
+    }
+  }
+  if (mode == MODE_LOSS) return MPDE_OK;
+  // 4. reduce the per-CTA partials, then the chain rule back to theta
+  float* gout = grad ? grad : gtmp;
+  {
+    ReduceParams rp;
+    rp.P = pl.P; rp.G = pl.G;
+    rp.part_a = pg; rp.out_a = gout; rp.out_a_stride = pl.P;
+    rp.part_b = (mode == MODE_HVP) ? ph : nullptr; rp.out_b = hv; rp.out_b_stride = pl.P;
+    rc = launch_simple(reduce_partials_kernel, (pl.P + 255) / 256, T, 256, 0, stream, rp);
+    if (rc) return rc;
+  }
+  {
+    ChainParams cp;
+    cp.W = pl.W; cp.L = pl.L; cp.OUT = pl.OUT; cp.log_scale = net->log_scale; cp.P = pl.P; cp.PH = pl.PH;
+    cp.theta = theta; cp.theta_stride = theta_stride; cp.v = v; cp.v_stride = v_stride;
+    cp.th = th; cp.th_stride = kp.th_stride; cp.thd = thd; cp.thd_stride = kp.thd_stride;
+    cp.g = gout; cp.g_stride = pl.P; cp.h = (mode == MODE_HVP) ? hv : nullptr; cp.h_stride = pl.P;
+    if (net->log_scale) {
+      rc = launch_simple(chain_kernel, T, 1, 256, 256 * sizeof(float), stream, cp);
+      if (rc) return rc;
+    }
+  }
+  return MPDE_OK;
+}
+
+}  // namespace mpde
+
+using namespace mpde;
+
+// =========================================================================== C ABI
+extern "C" {
+
+int mpde_param_count(const mpde_net_desc* net) {
+  if (!net) return -1;
+  return nat_count(net->layer_size, net->num_layers, net->out_dim, net->log_scale);
+}
+int mpde_num_point_sets(int k) { return k == MPDE_PDE_POISSON ? 2 : k == MPDE_PDE_TD_BURGERS ? 4 : k == MPDE_PDE_HYPER_ELASTICITY ? 3 : -1; }
+int mpde_num_terms(int k) { return mpde_num_point_sets(k); }
+int mpde_num_pde_params(int k) { return k == MPDE_PDE_POISSON ? NPRM_POISSON : k == MPDE_PDE_TD_BURGERS ? NPRM_BURGERS : k == MPDE_PDE_HYPER_ELASTICITY ? NPRM_HYPER : -1; }
+
+const char* mpde_status_string(int s) {
+  switch (s) {
+    case MPDE_OK: return "ok";
+    case MPDE_INVALID_ARG: return "invalid argument";
+    case MPDE_UNSUPPORTED_NET: return "unsupported network (SIREN, in_dim 2, layer_size in {32,64,128,256}, out_dim matching the PDE)";
+    case MPDE_WORKSPACE_TOO_SMALL: return "workspace too small";
+    case MPDE_CUDA_ERROR: return "CUDA error";
+  }
+  return "unknown status";
+}
+
+int64_t mpde_launch_count(void) { return (int64_t)g_launches.load(); }
+const char* mpde_backend(void) {
+#ifdef MPDE_EMU
+  return "emu";
+#else
+  return "cuda";
+#endif
+}
+
+size_t mpde_workspace_bytes(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, int mode) {
+  EvalPlan pl;
+  if (make_plan(net, pde, T, mode, mode == MODE_HVP, &pl)) return 0;
+  return pl.bytes;
+}
+
+int mpde_loss(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, const float* theta, int64_t theta_task_stride,
+              const mpde_points* points, const float* pde_params, float* loss, float* terms, float* domain_residual,
+              void* workspace, size_t workspace_bytes, void* stream) {
+  if (!loss && !terms && !domain_residual) return MPDE_INVALID_ARG;
+  const int nt = pde ? mpde_num_terms(pde->kind) : 0;
+  return run_eval(net, pde, T, MODE_LOSS, theta, theta_task_stride, nullptr, 0, points, pde_params, loss, 1, terms, nt,
+                  domain_residual, nullptr, nullptr, 0, workspace, workspace_bytes, stream);
+}
+
+int mpde_loss_grad(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, const float* theta,
+                   int64_t theta_task_stride, const mpde_points* points, const float* pde_params, float* loss,
+                   float* terms, float* grad, void* workspace, size_t workspace_bytes, void* stream) {
+  const int nt = pde ? mpde_num_terms(pde->kind) : 0;
+  return run_eval(net, pde, T, MODE_GRAD, theta, theta_task_stride, nullptr, 0, points, pde_params, loss, 1, terms, nt,
+                  nullptr, grad, nullptr, 1, workspace, workspace_bytes, stream);
+}
+
+int mpde_loss_hvp(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, const float* theta,
+                  int64_t theta_task_stride, const float* v, int64_t v_task_stride, const mpde_points* points,
+                  const float* pde_params, float* loss, float* terms, float* grad, float* hv, void* workspace,
+                  size_t workspace_bytes, void* stream) {
+  const int nt = pde ? mpde_num_terms(pde->kind) : 0;
+  return run_eval(net, pde, T, MODE_HVP, theta, theta_task_stride, v, v_task_stride, points, pde_params, loss, 1, terms,
+                  nt, nullptr, grad, hv, grad ? 1 : 0, workspace, workspace_bytes, stream);
+}
+
+// ------------------------------------------------------------------ field eval
+size_t mpde_field_eval_workspace_bytes(const mpde_net_desc* net, int T) {
+  if (check_net(net, 0) || T < 1) return 0;
+  const size_t PH = ph_count(net->layer_size, net->num_layers, net->out_dim);
+  return align_up((size_t)T * PH * sizeof(float)) + align_up((size_t)T * 4096 * MAX_SEG * sizeof(float)) + 512;
+}
+
+int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t theta_task_stride, const float* coords,
+                    int64_t coords_task_stride, int n, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_net(net, 0);
+  if (rc) return rc;
+  if (!theta || !coords || !out || T < 1 || n < 1) return MPDE_INVALID_ARG;
+  if (!workspace || workspace_bytes < mpde_field_eval_workspace_bytes(net, T)) return MPDE_WORKSPACE_TOO_SMALL;
+  const int W = net->layer_size, L = net->num_layers, OUT = net->out_dim;
+  const int PH = ph_count(W, L, OUT);
+  char* wsb = (char*)workspace;
+  wsb += (256 - ((uintptr_t)wsb & 255)) & 255;
+  Carver c(wsb, workspace_bytes);
+  const int T_prep = theta_task_stride == 0 ? 1 : T;
+  float* th = c.take((size_t)T * PH);
+  float* pt = c.take((size_t)T * 4096 * MAX_SEG);
+  PrepParams pp;
+  pp.W = W; pp.L = L; pp.OUT = OUT; pp.log_scale = net->log_scale; pp.P = mpde_param_count(net); pp.PH = PH; pp.T = T_prep;
+  pp.theta = theta; pp.theta_stride = theta_task_stride; pp.v = nullptr; pp.v_stride = 0; pp.th = th; pp.thd = nullptr;
+  int gx = grid_for(PH); if (gx > 64) gx = 64;
+  rc = launch_simple(prep_kernel, gx, T_prep, 256, 0, stream, pp);
+  if (rc) return rc;
+  const int kpde = (OUT == 2) ? PDE_EVAL2 : PDE_EVAL1;
+  KernelInfo ki;
+  rc = dispatch(W, kpde, MODE_LOSS, 0, nullptr, 0, 0, nullptr, &ki);
+  if (rc) return rc;
+  KParams kp;
+  kp.L = L; kp.P = pp.P; kp.PH = PH; kp.omega = net->omega; kp.T = T; kp.n_seg = 1;
+  kp.seg[0].pts = coords; kp.seg[0].task_stride = coords_task_stride; kp.seg[0].n = n;
+  kp.seg[0].head = (OUT == 2) ? HEAD_EVAL2 : HEAD_EVAL; kp.seg[0].coef = 0.f;
+  kp.seg[0].res_out = out; kp.seg[0].res_stride = (long long)n * OUT;
+  const int per_tile = 4 * ki.np;
+  const int tiles = (n + per_tile - 1) / per_tile;
+  kp.seg_tile_begin[0] = 0; kp.seg_tile_begin[1] = tiles;
+  static const float dummy_prm[16] = {0};
+  (void)dummy_prm;
+  kp.prm = theta; kp.nprm = 0;   // heads of the eval kernels never read pde params
+  kp.th = th; kp.th_stride = (T_prep == 1) ? 0 : PH; kp.thd = nullptr; kp.thd_stride = 0;
+  kp.scratch = nullptr; kp.scratch_per_cta = 0; kp.partial_g = nullptr; kp.partial_h = nullptr; kp.partial_terms = pt;
+  kp.want_grad = 0;
+  int G = tiles < 4096 ? tiles : 4096;
+  return dispatch(W, kpde, MODE_LOSS, 1, &kp, G, T, stream, nullptr);
+}
+
+// ------------------------------------------------------------------ K4
+int mpde_maml_inner_update(int T, int P, const float* theta, int64_t theta_task_stride, const float* grad,
+                           const float* alpha, float alpha_scalar, int softplus_lrs, float inner_lr, float clip,
+                           float* theta_next, float* gnorm, void* stream) {
+  if (T < 1 || P < 1 || !theta || !grad || !theta_next) return MPDE_INVALID_ARG;
+  InnerUpdParams p;
+  p.P = P; p.theta = theta; p.theta_stride = theta_task_stride; p.grad = grad; p.alpha = alpha; p.alpha_scalar = alpha_scalar;
+  p.softplus = softplus_lrs; p.inner_lr = inner_lr; p.clip = clip; p.theta_next = theta_next; p.gnorm = gnorm; p.gnorm_stride = 1;
+  return launch_simple(maml_inner_update_kernel, T, 1, 1024, 1024 * sizeof(float), stream, p);
+}
+
+size_t mpde_sumsq_workspace_bytes(int64_t n) { (void)n; return 1024 * sizeof(float) + 256; }
+int mpde_sumsq(const float* x, int64_t n, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!x || !out || n < 1) return MPDE_INVALID_ARG;
+  if (!workspace || workspace_bytes < mpde_sumsq_workspace_bytes(n)) return MPDE_WORKSPACE_TOO_SMALL;
+  int nb = grid_for(n, 256); if (nb > 1024) nb = 1024;
+  int rc = launch_simple(sumsq_stage1_kernel, nb, 1, 256, 256 * sizeof(float), stream, x, (long long)n, (float*)workspace);
+  if (rc) return rc;
+  return launch_simple(sumsq_stage2_kernel, 1, 1, 32, 0, stream, (const float*)workspace, nb, out);
+}
+int mpde_adam_step(float* x, const float* g, float* m, float* v, int64_t n, int t, float lr, float b1, float b2,
+                   float eps, const float* sumsq, float clip, void* stream) {
+  if (!x || !g || !m || !v || n < 1 || t < 1) return MPDE_INVALID_ARG;
+  const float bc1 = 1.f - powf(b1, (float)t), bc2 = 1.f - powf(b2, (float)t);
+  return launch_simple(adam_kernel, grid_for(n), 1, 256, 0, stream, x, g, m, v, (long long)n, lr, b1, b2, eps, bc1, bc2, sumsq, clip);
+}
+int mpde_sgd_step(float* x, const float* g, int64_t n, float lr, const float* sumsq, float clip, void* stream) {
+  if (!x || !g || n < 1) return MPDE_INVALID_ARG;
+  return launch_simple(sgd_kernel, grid_for(n), 1, 256, 0, stream, x, g, (long long)n, lr, sumsq, clip);
+}
+
+// ------------------------------------------------------------------ MAML rollout
+struct MamlWs {
+  size_t eval_bytes;
+  size_t n_thetas, n_grads, n_lam, n_gbar, n_tmp, n_galpha, n_gnorm, n_M, n_loss1;
+  size_t bytes;
+};
+static int maml_ws(const mpde_net_desc* net, const mpde_pde_desc* pi, const mpde_pde_desc* po, const mpde_maml_cfg* cfg,
+                   int T, bool outer, MamlWs* w) {
+  if (!net || !pi || !cfg || T < 1 || cfg->inner_steps < 1) return MPDE_INVALID_ARG;
+  const int K = cfg->inner_steps;
+  const size_t P = (size_t)mpde_param_count(net);
+  size_t e = mpde_workspace_bytes(net, pi, T, outer ? MODE_HVP : MODE_GRAD);
+  if (!e) return MPDE_UNSUPPORTED_NET;
+  if (outer) {
+    if (!po) return MPDE_INVALID_ARG;
+    size_t e2 = mpde_workspace_bytes(net, po, T, MODE_GRAD);
+    if (!e2) return MPDE_UNSUPPORTED_NET;
+    if (e2 > e) e = e2;
+    size_t e3 = mpde_workspace_bytes(net, pi, T, MODE_GRAD);
+    if (e3 > e) e = e3;
+  }
+  w->eval_bytes = align_up(e);
+  w->n_thetas = (size_t)K * T * P;                 // theta_1..theta_K
+  w->n_grads = outer ? (size_t)K * T * P : (size_t)T * P;   // g_k kept for the reverse sweep
+  w->n_lam = outer ? (size_t)T * P : 0;
+  w->n_gbar = outer ? (size_t)T * P : 0;
+  w->n_tmp = outer ? (size_t)T * P : 0;
+  w->n_galpha = outer ? (size_t)T * P : 0;
+  w->n_gnorm = (size_t)K * T;
+  w->n_M = (size_t)K * T;
+  w->n_loss1 = (size_t)T;
+  Carver c(nullptr, 0);
+  c.take(w->n_thetas); c.take(w->n_grads); c.take(w->n_lam); c.take(w->n_gbar); c.take(w->n_tmp); c.take(w->n_galpha);
+  c.take(w->n_gnorm); c.take(w->n_M); c.take(w->n_loss1);
+  w->bytes = w->eval_bytes + c.off + 512;
+  return MPDE_OK;
+}
+
+size_t mpde_maml_workspace_bytes(const mpde_net_desc* net, const mpde_pde_desc* pde_inner, const mpde_pde_desc* pde_outer,
+                                 const mpde_maml_cfg* cfg, int T) {
+  MamlWs w;
+  if (maml_ws(net, pde_inner, pde_outer, cfg, T, pde_outer != nullptr, &w)) return 0;
+  return w.bytes;
+}
+
+static int maml_impl(const mpde_net_desc* net, const mpde_pde_desc* pi, const mpde_pde_desc* po, const mpde_maml_cfg* cfg,
+                     int T, const float* theta0, const float* inner_lrs, const mpde_points* inner_points,
+                     const mpde_points* outer_points, const mpde_points* final_points, const mpde_points* aux_points,
+                     const float* pde_params, float grad_scale, float* meta_grad_theta, float* meta_grad_lrs,
+                     float* losses, float* meta_losses, float* aux_terms, float* theta_final, bool outer,
+                     void* workspace, size_t workspace_bytes, void* stream) {
+  MamlWs w;
+  int rc = maml_ws(net, pi, po, cfg, T, outer, &w);
+  if (rc) return rc;
+  if (!theta0 || !inner_points || !final_points || !pde_params || !losses) return MPDE_INVALID_ARG;
+  if (outer && (!outer_points || !aux_points || !meta_grad_theta || !meta_losses)) return MPDE_INVALID_ARG;
+  if (!workspace || workspace_bytes < w.bytes) return MPDE_WORKSPACE_TOO_SMALL;
+  const int K = cfg->inner_steps;
+  const int P = mpde_param_count(net);
+  const long long TP = (long long)T * P;
+  char* wsb = (char*)workspace;
+  wsb += (256 - ((uintptr_t)wsb & 255)) & 255;
+  void* eval_ws = wsb;
+  Carver c(wsb + w.eval_bytes, workspace_bytes - w.eval_bytes);
+  float* thetas = c.take(w.n_thetas); float* grads = c.take(w.n_grads); float* lam = c.take(w.n_lam);
+  float* gbar = c.take(w.n_gbar); float* tmp = c.take(w.n_tmp); float* galpha = c.take(w.n_galpha);
+  float* gnorm = c.take(w.n_gnorm); float* Mk = c.take(w.n_M); float* loss1 = c.take(w.n_loss1);
+  (void)loss1;
+  const int nterms = mpde_num_terms(pi->kind);
+
+  // ---- forward sweep: K inner SGD steps (maml.py:132-155) ----
+  for (int k = 0; k < K; ++k) {
+    const float* th_k = (k == 0) ? theta0 : thetas + (size_t)(k - 1) * TP;
+    const long long st_k = (k == 0) ? 0 : P;
+    float* g_k = outer ? grads + (size_t)k * TP : grads;
+    rc = run_eval(net, pi, T, MODE_GRAD, th_k, st_k, nullptr, 0, &inner_points[k], pde_params, losses + k, K + 1,
+                  nullptr, 0, nullptr, g_k, nullptr, 1, eval_ws, w.eval_bytes, stream);
+    if (rc) return rc;
+    InnerUpdParams up;
+    up.P = P; up.theta = th_k; up.theta_stride = st_k; up.grad = g_k;
+    up.alpha = inner_lrs ? inner_lrs + (size_t)k * P : nullptr; up.alpha_scalar = 1.0f; up.softplus = cfg->softplus_lrs;
+    up.inner_lr = cfg->inner_lr; up.clip = cfg->inner_grad_clip;
+    up.theta_next = thetas + (size_t)k * TP; up.gnorm = gnorm + (size_t)k * T; up.gnorm_stride = 1;
+    rc = launch_simple(maml_inner_update_kernel, T, 1, 1024, 1024 * sizeof(float), stream, up);
+    if (rc) return rc;
+  }
+  const float* th_K = thetas + (size_t)(K - 1) * TP;
+  // final inner loss (maml.py:158) -> losses[:, K]
+  rc = run_eval(net, pi, T, MODE_LOSS, th_K, P, nullptr, 0, final_points, pde_params, losses + K, K + 1, nullptr, 0,
+                nullptr, nullptr, nullptr, 0, eval_ws, w.eval_bytes, stream);
+  if (rc) return rc;
+  if (theta_final) {
+    rc = launch_simple(axpby_kernel, grid_for(TP), 1, 256, 0, stream, theta_final, th_K, 1.0f, 0.0f, TP);
+    if (rc) return rc;
+  }
+  if (!outer) return MPDE_OK;
+
+  // aux-only outer loss at theta_K (maml.py:192)
+  if (aux_terms) {
+    rc = run_eval(net, po, T, MODE_LOSS, th_K, P, nullptr, 0, aux_points, pde_params, nullptr, 0, aux_terms, nterms,
+                  nullptr, nullptr, nullptr, 0, eval_ws, w.eval_bytes, stream);
+    if (rc) return rc;
+  }
+
+  // ---- reverse sweep ----
+  rc = launch_simple(fill_kernel, grid_for(TP), 1, 256, 0, stream, lam, 0.0f, TP);
+  if (rc) return rc;
+  float coef = 1.0f;   // decay^(K-k-1)
+  for (int k = K - 1; k >= 0; --k) {
+    const float* th_k1 = thetas + (size_t)k * TP;
+    // (M_{k+1}, grad M_{k+1}) at theta_{k+1} on the outer points of step k
+    rc = run_eval(net, po, T, MODE_GRAD, th_k1, P, nullptr, 0, &outer_points[k], pde_params, Mk + k, K, nullptr, 0,
+                  nullptr, tmp, nullptr, 1, eval_ws, w.eval_bytes, stream);
+    if (rc) return rc;
+    InnerVjpParams vp;
+    vp.P = P; vp.lam = lam; vp.add = tmp; vp.c_add = coef; vp.grad = grads + (size_t)k * TP;
+    vp.alpha = inner_lrs ? inner_lrs + (size_t)k * P : nullptr; vp.alpha_scalar = 1.0f; vp.softplus = cfg->softplus_lrs;
+    vp.gnorm = gnorm + (size_t)k * T; vp.gnorm_stride = 1; vp.inner_lr = cfg->inner_lr; vp.clip = cfg->inner_grad_clip;
+    vp.gbar = gbar; vp.galpha = (inner_lrs && meta_grad_lrs) ? galpha : nullptr;
+    rc = launch_simple(maml_inner_vjp_kernel, T, 1, 1024, 1024 * sizeof(float), stream, vp);
+    if (rc) return rc;
+    if (vp.galpha) {
+      rc = launch_simple(task_sum_kernel, grid_for(P), 1, 256, 0, stream, meta_grad_lrs + (size_t)k * P, (const float*)galpha, T, (long long)P, grad_scale);
+      if (rc) return rc;
+    }
+    const float* th_k = (k == 0) ? theta0 : thetas + (size_t)(k - 1) * TP;
+    const long long st_k = (k == 0) ? 0 : P;
+    // H(theta_k) gbar on the inner points of step k
+    rc = run_eval(net, pi, T, MODE_HVP, th_k, st_k, gbar, P, &inner_points[k], pde_params, nullptr, 0, nullptr, 0,
+                  nullptr, nullptr, tmp, 0, eval_ws, w.eval_bytes, stream);
+    if (rc) return rc;
+    rc = launch_simple(axpby_kernel, grid_for(TP), 1, 256, 0, stream, lam, (const float*)tmp, 1.0f, 1.0f, TP);
+    if (rc) return rc;
+    coef *= cfg->outer_loss_decay;
+  }
+  rc = launch_simple(task_sum_kernel, grid_for(P), 1, 256, 0, stream, meta_grad_theta, (const float*)lam, T, (long long)P, grad_scale);
+  if (rc) return rc;
+  // Mk is laid out [T][K] via (ptr + k, stride K)
+  return launch_simple(meta_loss_kernel, (T + 127) / 128, 1, 128, 0, stream, meta_losses, (const float*)Mk, T, K, cfg->outer_loss_decay);
+}
+
+int mpde_maml_outer(const mpde_net_desc* net, const mpde_pde_desc* pde_inner, const mpde_pde_desc* pde_outer,
+                    const mpde_maml_cfg* cfg, int T, const float* theta0, const float* inner_lrs,
+                    const mpde_points* inner_points, const mpde_points* outer_points, const mpde_points* final_points,
+                    const mpde_points* aux_points, const float* pde_params, float grad_scale, float* meta_grad_theta,
+                    float* meta_grad_lrs, float* losses, float* meta_losses, float* aux_terms, float* theta_final,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  if (!pde_outer) return MPDE_INVALID_ARG;
+  return maml_impl(net, pde_inner, pde_outer, cfg, T, theta0, inner_lrs, inner_points, outer_points, final_points,
+                   aux_points, pde_params, grad_scale, meta_grad_theta, meta_grad_lrs, losses, meta_losses, aux_terms,
+                   theta_final, true, workspace, workspace_bytes, stream);
+}
+
+int mpde_maml_adapt(const mpde_net_desc* net, const mpde_pde_desc* pde_inner, const mpde_maml_cfg* cfg, int T,
+                    const float* theta0, const float* inner_lrs, const mpde_points* inner_points,
+                    const mpde_points* final_points, const float* pde_params, float* theta_final, float* losses,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  return maml_impl(net, pde_inner, nullptr, cfg, T, theta0, inner_lrs, inner_points, nullptr, final_points, nullptr,
+                   pde_params, 0.f, nullptr, nullptr, losses, nullptr, nullptr, theta_final, false, workspace,
+                   workspace_bytes, stream);
+}
+
+// ------------------------------------------------------------------ LEAP rollout
+struct LeapWs { size_t eval_bytes, n_tp, n_T, bytes; };
+static int leap_ws(const mpde_net_desc* net, const mpde_pde_desc* pde, const mpde_leap_cfg* cfg, int T, LeapWs* w) {
+  if (!net || !pde || !cfg || T < 1 || cfg->inner_steps < 1) return MPDE_INVALID_ARG;
+  size_t e = mpde_workspace_bytes(net, pde, T, MODE_GRAD);
+  if (!e) return MPDE_UNSUPPORTED_NET;
+  w->eval_bytes = align_up(e);
+  w->n_tp = (size_t)T * mpde_param_count(net);
+  w->n_T = (size_t)T;
+  Carver c(nullptr, 0);
+  for (int i = 0; i < 6; ++i) c.take(w->n_tp);   // theta_a, theta_b, grad, accum, m, v
+  c.take(w->n_T); c.take(w->n_T);
+  w->bytes = w->eval_bytes + c.off + 512;
+  return MPDE_OK;
+}
+size_t mpde_leap_workspace_bytes(const mpde_net_desc* net, const mpde_pde_desc* pde, const mpde_leap_cfg* cfg, int T) {
+  LeapWs w;
+  if (leap_ws(net, pde, cfg, T, &w)) return 0;
+  return w.bytes;
+}
+
+int mpde_leap_outer(const mpde_net_desc* net, const mpde_pde_desc* pde, const mpde_leap_cfg* cfg, int T,
+                    const float* theta0, const mpde_points* loss0_points, const mpde_points* step_points,
+                    const mpde_points* new_points, const float* pde_params, float grad_scale, float* meta_grad,
+                    float* losses, float* theta_final, void* workspace, size_t workspace_bytes, void* stream) {
+  LeapWs w;
+  int rc = leap_ws(net, pde, cfg, T, &w);
+  if (rc) return rc;
+  if (!theta0 || !loss0_points || !step_points || !new_points || !pde_params || !meta_grad || !losses) return MPDE_INVALID_ARG;
+  if (!workspace || workspace_bytes < w.bytes) return MPDE_WORKSPACE_TOO_SMALL;
+  const int K = cfg->inner_steps, P = mpde_param_count(net);
+  const long long TP = (long long)T * P;
+  char* wsb = (char*)workspace;
+  wsb += (256 - ((uintptr_t)wsb & 255)) & 255;
+  void* eval_ws = wsb;
+  Carver c(wsb + w.eval_bytes, workspace_bytes - w.eval_bytes);
+  float* th_a = c.take(w.n_tp); float* th_b = c.take(w.n_tp); float* grad = c.take(w.n_tp); float* accum = c.take(w.n_tp);
+  float* m = c.take(w.n_tp); float* v = c.take(w.n_tp); float* lossk = c.take(w.n_T); float* dummy = c.take(w.n_T);
+  (void)dummy;
+  // loss0 (leap.py:126)
+  rc = run_eval(net, pde, T, MODE_LOSS, theta0, 0, nullptr, 0, loss0_points, pde_params, losses, K + 1, nullptr, 0, nullptr,
+                nullptr, nullptr, 0, eval_ws, w.eval_bytes, stream);
+  if (rc) return rc;
+  rc = launch_simple(fill_kernel, grid_for(TP), 1, 256, 0, stream, accum, 0.0f, TP); if (rc) return rc;
+  if (cfg->inner_opt == 1) {
+    rc = launch_simple(fill_kernel, grid_for(TP), 1, 256, 0, stream, m, 0.0f, TP); if (rc) return rc;
+    rc = launch_simple(fill_kernel, grid_for(TP), 1, 256, 0, stream, v, 0.0f, TP); if (rc) return rc;
+  }
+  const float* th_k = theta0; long long st_k = 0;
+  float* th_next = th_a;
+  for (int k = 0; k < K; ++k) {
+    rc = run_eval(net, pde, T, MODE_GRAD, th_k, st_k, nullptr, 0, &step_points[k], pde_params, lossk, 1, nullptr, 0, nullptr,
+                  grad, nullptr, 1, eval_ws, w.eval_bytes, stream);
+    if (rc) return rc;
+    LeapStepParams sp;
+    sp.P = P; sp.theta = th_k; sp.theta_stride = st_k; sp.grad = grad; sp.theta_next = th_next; sp.m = m; sp.v = v;
+    sp.inner_opt = cfg->inner_opt; sp.t_step = k + 1; sp.lr = cfg->inner_lr; sp.clip = cfg->inner_grad_clip;
+    sp.b1 = cfg->beta1; sp.b2 = cfg->beta2; sp.eps = cfg->eps;
+    rc = launch_simple(leap_inner_update_kernel, T, 1, 1024, 1024 * sizeof(float), stream, sp);
+    if (rc) return rc;
+    // new_loss on fresh points (leap.py:93) -> losses[:, k+1]
+    rc = run_eval(net, pde, T, MODE_LOSS, th_next, P, nullptr, 0, &new_points[k], pde_params, losses + (k + 1), K + 1, nullptr,
+                  0, nullptr, nullptr, nullptr, 0, eval_ws, w.eval_bytes, stream);
+    if (rc) return rc;
+    LeapIncParams ip;
+    ip.P = P; ip.theta = th_k; ip.theta_stride = st_k; ip.theta_next = th_next; ip.grad = grad;
+    ip.loss = lossk; ip.loss_stride = 1; ip.new_loss = losses + (k + 1); ip.new_loss_stride = K + 1; ip.accum = accum;
+    ip.norm = cfg->norm; ip.loss_in_distance = cfg->loss_in_distance; ip.stabilize = cfg->stabilize;
+    rc = launch_simple(leap_increment_kernel, T, 1, 1024, 1024 * sizeof(float), stream, ip);
+    if (rc) return rc;
+    th_k = th_next; st_k = P;
+    th_next = (th_next == th_a) ? th_b : th_a;
+  }
+  if (theta_final) {
+    rc = launch_simple(axpby_kernel, grid_for(TP), 1, 256, 0, stream, theta_final, th_k, 1.0f, 0.0f, TP);
+    if (rc) return rc;
+  }
+  return launch_simple(task_sum_kernel, grid_for(P), 1, 256, 0, stream, meta_grad, (const float*)accum, T, (long long)P, grad_scale);
+}
+
+}  // extern "C"

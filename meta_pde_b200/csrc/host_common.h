@@ -1,0 +1,35 @@
+// host_common.h -- host-side glue shared by the translation units of libmetapde_b200.
+#pragma once
+#include "compat.cuh"
+#include "pde_kernels.cuh"
+#include <atomic>
+
+namespace mpde {
+
+struct KernelInfo {
+  int nt;            // threads per CTA
+  size_t smem;       // dynamic shared memory bytes
+  int occ;           // resident CTAs per SM
+  int np;            // points per channel-jet tile (value-only tiles hold 4*np)
+};
+
+extern std::atomic<long long> g_launches;
+int device_sm_count();
+
+// op 0: fill *info; op 1: launch.  One definition per width (inst_w*.cu) so the widths compile in parallel.
+int dispatch_w32(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+int dispatch_w64(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+int dispatch_w128(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+int dispatch_w256(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+
+#ifdef MPDE_EMU
+#define MPDE_LAUNCH(kfn, grid, block, smem, stream, ...)                                   \
+  do { ::mpde::g_launches++; emu::launch(grid, block, smem, [=]() { kfn(__VA_ARGS__); }); } while (0)
+#define MPDE_CHECK_LAUNCH() 0
+#else
+#define MPDE_LAUNCH(kfn, grid, block, smem, stream, ...)                                   \
+  do { ::mpde::g_launches++; kfn<<<grid, block, smem, (cudaStream_t)(stream)>>>(__VA_ARGS__); } while (0)
+#define MPDE_CHECK_LAUNCH() (cudaGetLastError() != cudaSuccess)
+#endif
+
+}  // namespace mpde

@@ -1,0 +1,56 @@
+// inst.cuh -- instantiates pde_kernel for one width and dispatches on (pde, mode).
+#pragma once
+#include "host_common.h"
+#include <mutex>
+
+namespace mpde {
+
+template <int W, int NTY, int PDE, int MODE>
+int run_inst(int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  typedef Geo<W, NTY> G;
+  auto kfn = pde_kernel<W, NTY, PDE, MODE>;
+  const size_t smem = G::smem_bytes(MODE);
+  static int occ = 0;
+#ifndef MPDE_EMU
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&]() {
+    attr_err = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (attr_err == cudaSuccess) attr_err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, G::NT, smem);
+  });
+  if (attr_err != cudaSuccess || occ < 1) return 4;
+#else
+  occ = 2;
+#endif
+  if (op == 0) {
+    info->nt = G::NT; info->smem = smem; info->occ = occ; info->np = G::NP;
+    return 0;
+  }
+  KParams kp = *p;
+  MPDE_LAUNCH(kfn, dim3(gx, gy, 1), dim3(G::NT, 1, 1), smem, stream, kp);
+  return MPDE_CHECK_LAUNCH() ? 4 : 0;
+}
+
+template <int W, int NTY, int PDE>
+int run_mode(int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  switch (mode) {
+    case MODE_LOSS: return run_inst<W, NTY, PDE, MODE_LOSS>(op, p, gx, gy, stream, info);
+    case MODE_GRAD: return run_inst<W, NTY, PDE, MODE_GRAD>(op, p, gx, gy, stream, info);
+    case MODE_HVP:  return run_inst<W, NTY, PDE, MODE_HVP>(op, p, gx, gy, stream, info);
+  }
+  return 1;
+}
+
+template <int W, int NTY>
+int run_width(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  switch (pde) {
+    case PDE_POISSON: return run_mode<W, NTY, PDE_POISSON>(mode, op, p, gx, gy, stream, info);
+    case PDE_BURGERS: return run_mode<W, NTY, PDE_BURGERS>(mode, op, p, gx, gy, stream, info);
+    case PDE_HYPER:   return run_mode<W, NTY, PDE_HYPER>(mode, op, p, gx, gy, stream, info);
+    case PDE_EVAL1:   return run_inst<W, NTY, PDE_EVAL1, MODE_LOSS>(op, p, gx, gy, stream, info);
+    case PDE_EVAL2:   return run_inst<W, NTY, PDE_EVAL2, MODE_LOSS>(op, p, gx, gy, stream, info);
+  }
+  return 1;
+}
+
+}  // namespace mpde
