@@ -66,7 +66,7 @@ extern __shared__ __align__(16) unsigned char mpde_smem_raw[];
 __device__ __forceinline__ unsigned char* mpde_smem() { return mpde_smem_raw; }
 // accurate (range-reduced) sincosf: arguments reach |omega*z| ~ 1e2 and the
 // parity bar is rel 1e-4 on Hessian-vector products -- never __sinf/__cosf.
-__device__ __forceinline__ void mpde_sincosf(float x, float* s, float* c) { sincosf(x, s, c); }
+__host__ __device__ __forceinline__ void mpde_sincosf(float x, float* s, float* c) { sincosf(x, s, c); }
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
   unsigned d = (unsigned)__cvta_generic_to_shared(dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(src) : "memory");

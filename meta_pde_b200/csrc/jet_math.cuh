@@ -238,23 +238,26 @@ MPDE_HD float head_eval(const float* u, float x0, float x1, const float* prm, fl
     *res = r;
     return r * r;
   } else if (HEAD == HEAD_HYPER_DOMAIN) {
-    // u[o*3 + c]; F = I + grad u
+    // u[o*3 + c]; grad u = [[a, b], [c, d]], F = I + grad u, J = det F, Ic = tr(F F^T).
+    // psi = (mu/2)(Ic/J - 2) + (kappa/2)(J - 1)^2 is evaluated in the algebraically identical,
+    // cancellation-free form  Ic - 2J = (a - d)^2 + (b + c)^2,  J - 1 = a + d + a d - b c
+    // (the literal float32 form loses ~4 digits near F = I, where the reference's own f32 result is noise).
     const float E = prm[2];
-    const float mu = E / (2.f * (1.f + 0.49f)), kap = E / (3.f * (1.f - 2.f * 0.49f));
-    const float F11 = 1.f + u[1], F12 = u[2], F21 = u[4], F22 = 1.f + u[5];
-    const float J = F11 * F22 - F12 * F21;
-    const float I = F11 * F11 + F12 * F12 + F21 * F21 + F22 * F22;
-    const float iJ = 1.f / J;
-    const float psi = 0.5f * mu * (I * iJ - 2.f) + 0.5f * kap * (J - 1.f) * (J - 1.f);
-    const float A = 0.5f * mu;
-    const float cI = A * I * iJ * iJ, cK = kap * (J - 1.f);
-    // d psi / dF = A (2F/J - (I/J^2) cof) + kap (J-1) cof ; cof = [[F22,-F21],[-F12,F11]]
-    const float s = cK - cI;
+    const float A = 0.5f * E / (2.f * (1.f + 0.49f)), kap = E / (3.f * (1.f - 2.f * 0.49f));
+    const float a = u[1], b = u[2], c = u[4], d = u[5];
+    const float m = a + d + a * d - b * c;   // J - 1
+    const float J = 1.f + m, iJ = 1.f / J;
+    const float e1 = a - d, e2 = b + c;
+    const float N = e1 * e1 + e2 * e2;
+    const float psi = A * N * iJ + 0.5f * kap * m * m;
+    // d psi / dx = A (N_x / J - N J_x / J^2) + kappa m J_x ; J_a = 1+d, J_d = 1+a, J_b = -c, J_c = -b
+    const float s = kap * m - A * N * iJ * iJ;
+    const float t1 = 2.f * A * iJ;
     ub[0] = 0.f; ub[3] = 0.f;
-    ub[1] = coef * (2.f * A * F11 * iJ + s * F22);
-    ub[2] = coef * (2.f * A * F12 * iJ - s * F21);
-    ub[4] = coef * (2.f * A * F21 * iJ - s * F12);
-    ub[5] = coef * (2.f * A * F22 * iJ + s * F11);
+    ub[1] = coef * (t1 * e1 + s * (1.f + d));
+    ub[2] = coef * (t1 * e2 - s * c);
+    ub[4] = coef * (t1 * e2 - s * b);
+    ub[5] = coef * (-t1 * e1 + s * (1.f + a));
     *res = psi;
     return psi;
   } else if (HEAD == HEAD_EVAL || HEAD == HEAD_EVAL2) {
@@ -305,24 +308,22 @@ MPDE_HD void head_tangent(const float* u, const float* ud, float x0, float x1, c
     ubd[3] = -c2 * rd * ire;
   } else if (HEAD == HEAD_HYPER_DOMAIN) {
     const float E = prm[2];
-    const float mu = E / (2.f * (1.f + 0.49f)), kap = E / (3.f * (1.f - 2.f * 0.49f));
-    const float F11 = 1.f + u[1], F12 = u[2], F21 = u[4], F22 = 1.f + u[5];
-    const float D11 = ud[1], D12 = ud[2], D21 = ud[4], D22 = ud[5];
-    const float J = F11 * F22 - F12 * F21;
-    const float I = F11 * F11 + F12 * F12 + F21 * F21 + F22 * F22;
-    const float iJ = 1.f / J;
-    const float A = 0.5f * mu;
-    const float Jd = F22 * D11 - F21 * D12 - F12 * D21 + F11 * D22;
-    const float Id = 2.f * (F11 * D11 + F12 * D12 + F21 * D21 + F22 * D22);
-    const float cI = A * I * iJ * iJ, cK = kap * (J - 1.f);
-    const float s = cK - cI;
-    const float sd = kap * Jd - A * (Id * iJ * iJ - 2.f * I * Jd * iJ * iJ * iJ);
+    const float A = 0.5f * E / (2.f * (1.f + 0.49f)), kap = E / (3.f * (1.f - 2.f * 0.49f));
+    const float a = u[1], b = u[2], c = u[4], d = u[5];
+    const float ad = ud[1], bd = ud[2], cd = ud[4], dd = ud[5];
+    const float m = a + d + a * d - b * c;
+    const float J = 1.f + m, iJ = 1.f / J;
+    const float e1 = a - d, e2 = b + c, e1d = ad - dd, e2d = bd + cd;
+    const float N = e1 * e1 + e2 * e2, Nd = 2.f * (e1 * e1d + e2 * e2d);
+    const float Jd = (1.f + d) * ad + (1.f + a) * dd - c * bd - b * cd;
+    const float s = kap * m - A * N * iJ * iJ;
+    const float sd = kap * Jd - A * (Nd * iJ * iJ - 2.f * N * Jd * iJ * iJ * iJ);
     const float t1 = 2.f * A * iJ, t1d = -2.f * A * Jd * iJ * iJ;
     ubd[0] = 0.f; ubd[3] = 0.f;
-    ubd[1] = coef * (t1 * D11 + t1d * F11 + sd * F22 + s * D22);
-    ubd[2] = coef * (t1 * D12 + t1d * F12 - sd * F21 - s * D21);
-    ubd[4] = coef * (t1 * D21 + t1d * F21 - sd * F12 - s * D12);
-    ubd[5] = coef * (t1 * D22 + t1d * F22 + sd * F11 + s * D11);
+    ubd[1] = coef * (t1 * e1d + t1d * e1 + sd * (1.f + d) + s * dd);
+    ubd[2] = coef * (t1 * e2d + t1d * e2 - sd * c - s * cd);
+    ubd[4] = coef * (t1 * e2d + t1d * e2 - sd * b - s * bd);
+    ubd[5] = coef * (-t1 * e1d - t1d * e1 + sd * (1.f + a) + s * ad);
   } else if (HEAD == HEAD_EVAL || HEAD == HEAD_EVAL2) {
     for (int o = 0; o < HeadTraits<HEAD>::OUT; ++o) ubd[o] = 0.f;
   } else {

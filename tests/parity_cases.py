@@ -1,0 +1,218 @@
+"""Parity checkers shared by the emulator (CPU) and GPU test modules.
+
+Each checker runs the kernels through the C ABI (``K`` = meta_pde_b200._abi.Kernels bound to
+either the CUDA library or the test-only emulator build) and the float64 oracle on the same
+seeded inputs, and asserts the north-star tolerance: relative 1e-4 (vector rel-L2) on
+residuals, losses, inner-updated params and outer gradients.
+"""
+import torch
+
+from helpers import oracle_params, oracle_points, rel_l2, synthetic
+from meta_pde_b200._abi import PDE_OUT_DIM, PDE_TERMS
+from oracle import meta as ometa
+from oracle.field import make_field_fn, unflatten_params
+from oracle import pdes as opdes
+
+TOL = 1e-4  # BASELINE.json north_star: "relative 1e-4 on residuals, losses, inner-updated params and outer gradients"
+OMEGA = 30.0
+
+
+def _tol(name, theta_K, theta0):
+    """1e-4, except for the UPDATE theta_K - theta_0, whose float32 resolution is eps32 * |theta| / |update|."""
+    if name != "theta_delta":
+        return TOL
+    d = (theta_K.double() - theta0.double()).norm().item()
+    return max(TOL, 8 * 6e-8 * theta_K.double().norm().item() / max(d, 1e-300))
+
+
+def _dev(K, x):
+    return x.to(K.device)
+
+
+def make_problem(pde, W, L, n, T, seed=0, per_task_theta=True, set_sizes=None):
+    out = PDE_OUT_DIM[pde]
+    theta = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    if per_task_theta:
+        g = torch.Generator().manual_seed(seed + 100)
+        theta = torch.stack([theta * (1.0 + 0.02 * t) + 1e-3 * torch.randn(theta.numel(), generator=g) for t in range(T)])
+    sizes = set_sizes if set_sizes is not None else synthetic.default_set_sizes(pde, n)
+    sets, prm = synthetic.make_tasks(pde, T, sizes, seed=seed + 1)
+    return theta, sets, prm
+
+
+def oracle_loss_fn(pde, W, L, bc_weight=1.0):
+    return ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, OMEGA, True, PDE_OUT_DIM[pde]), bc_weight)
+
+
+def check_loss_grad_hvp(K, pde, W, L, n, T, bc_weight=1.0, seed=0, set_sizes=None, per_task_theta=True):
+    theta, sets, prm = make_problem(pde, W, L, n, T, seed, per_task_theta, set_sizes)
+    P = theta.shape[-1]
+    v = torch.randn(T, P, generator=torch.Generator().manual_seed(seed + 7))
+    net = K.net_desc(L, W, PDE_OUT_DIM[pde], OMEGA, True)
+    dsets = [_dev(K, s) for s in sets]
+    loss0, terms0, res = K.loss(net, pde, bc_weight, _dev(K, theta), dsets, _dev(K, prm), T, want_residual=True)
+    loss1, terms1, grad1 = K.loss_grad(net, pde, bc_weight, _dev(K, theta), dsets, _dev(K, prm), T)
+    loss2, terms2, grad2, hv = K.loss_hvp(net, pde, bc_weight, _dev(K, theta), _dev(K, v), dsets, _dev(K, prm), T)
+    lf = oracle_loss_fn(pde, W, L, bc_weight)
+    errs = {}
+    for t in range(T):
+        th0 = theta[t] if theta.dim() == 2 else theta
+        th = th0.double().requires_grad_(True)
+        pts, prm_t = oracle_points(pde, sets, t), oracle_params(pde, prm, t)
+        l, aux = lf(th, pts, prm_t)
+        (g,) = torch.autograd.grad(l, th, create_graph=True)
+        (h,) = torch.autograd.grad((g * v[t].double()).sum(), th)
+        ot = torch.stack([aux[k].detach() for k in PDE_TERMS[pde]])
+        # per-point residual / energy density
+        params = unflatten_params(th0.double(), [W] * L, 2, PDE_OUT_DIM[pde], True)
+        ffn = make_field_fn(params, PDE_OUT_DIM[pde], OMEGA)
+        if pde == "poisson":
+            r = opdes.poisson_residual(ffn, pts[1], prm_t[0])
+        elif pde == "td_burgers":
+            r = opdes.burgers_rhs(ffn, pts[3], prm_t)
+        else:
+            r = opdes.hyper_energy_density(ffn, pts[5], prm_t)
+        for name, got, want in [
+            ("loss0", loss0[t], l), ("loss1", loss1[t], l), ("loss2", loss2[t], l),
+            ("terms0", terms0[t], ot), ("terms1", terms1[t], ot), ("terms2", terms2[t], ot),
+            ("residual", res[t], r), ("grad1", grad1[t], g), ("grad2", grad2[t], g), ("hv", hv[t], h),
+        ]:
+            e = rel_l2(got.detach().cpu(), want.detach())
+            errs[name] = max(errs.get(name, 0.0), e)
+    bad = {k: e for k, e in errs.items() if not (e < TOL)}
+    assert not bad, f"{pde} W={W} L={L} n={n}: rel errors above {TOL}: {bad} (all: {errs})"
+    return errs
+
+
+def make_maml_data(pde, n_in, n_out, T, K_steps, seed):
+    """Per-step inner/outer point sets + final/aux sets, ABI layout (each a list of [T, n, 2] tensors)."""
+    si, so = synthetic.default_set_sizes(pde, n_in), synthetic.default_set_sizes(pde, n_out)
+    inner, outer = [], []
+    prm = None
+    for k in range(K_steps):
+        s, prm_k = synthetic.make_tasks(pde, T, si, seed=seed + 10 * k + 1)
+        inner.append(s)
+        prm = prm_k if prm is None else prm
+        s2, _ = synthetic.make_tasks(pde, T, so, seed=seed + 10 * k + 2)
+        outer.append(s2)
+    final, _ = synthetic.make_tasks(pde, T, si, seed=seed + 1001)
+    aux, _ = synthetic.make_tasks(pde, T, so, seed=seed + 1002)
+    return inner, outer, final, aux, prm
+
+
+def check_maml(K, pde, W, L, n, T, K_steps=2, inner_lr=1e-3, clip=1e14, decay=0.1, lr_tree=True, seed=0, bc_weight=1.0):
+    out = PDE_OUT_DIM[pde]
+    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    P = theta0.numel()
+    inner, outer, final, aux, prm = make_maml_data(pde, n, n, T, K_steps, seed)
+    g = torch.Generator().manual_seed(seed + 55)
+    lrs = (1.0 + 0.3 * torch.randn(K_steps, P, generator=g)) if lr_tree else None
+    cfg = dict(inner_steps=K_steps, inner_lr=inner_lr, inner_grad_clip=clip, softplus_lrs=True, outer_loss_decay=decay)
+    net = K.net_desc(L, W, out, OMEGA, True)
+    d = lambda sets: [_dev(K, s) for s in sets]
+    got = K.maml_outer(net, pde, bc_weight, cfg, _dev(K, theta0), _dev(K, lrs) if lrs is not None else None,
+                       [d(s) for s in inner], [d(s) for s in outer], d(final), d(aux), _dev(K, prm), T,
+                       want_theta_final=True)
+    # oracle
+    lf = oracle_loss_fn(pde, W, L, bc_weight)
+    ocfg = ometa.MamlCfg(K_steps, inner_lr, clip, True, decay)
+    tasks = []
+    for t in range(T):
+        tasks.append(ometa.MamlTask(oracle_params(pde, prm, t), [oracle_points(pde, s, t) for s in inner],
+                                    [oracle_points(pde, s, t) for s in outer], oracle_points(pde, final, t),
+                                    oracle_points(pde, aux, t)))
+    olrs = lrs.double() if lrs is not None else torch.ones(K_steps, 1, dtype=torch.float64).expand(K_steps, P).contiguous()
+    # scalar-lr variant of the reference uses np.ones(K): softplus(1.0) on every parameter == lr tree of ones
+    outs = [ometa.maml_single_task_grad_and_losses(ocfg, lf, theta0.double(), tk, olrs) for tk in tasks]
+    g_theta = torch.stack([o[0][0] for o in outs]).mean(0)
+    g_lrs = torch.stack([o[0][1] for o in outs]).mean(0)
+    losses = torch.stack([o[1] for o in outs])
+    meta = torch.stack([o[2][0] for o in outs])
+    auxd = torch.stack([torch.stack([o[2][1][k] for k in PDE_TERMS[pde]]) for o in outs])
+    theta_K = torch.stack([o[3][-1] for o in outs])
+    clipped = []
+    errs = {
+        "g_theta": rel_l2(got["g_theta"].cpu(), g_theta),
+        "losses": rel_l2(got["losses"].cpu(), losses),
+        "meta_losses": rel_l2(got["meta_losses"].cpu(), meta),
+        "aux_terms": rel_l2(got["aux_terms"].cpu(), auxd),
+        "theta_final": rel_l2(got["theta_final"].cpu(), theta_K),
+        # inner-updated params: compare the UPDATE (theta_K - theta_0), the part the kernels produce
+        "theta_delta": rel_l2(got["theta_final"].cpu().double() - theta0.double(), theta_K - theta0.double()),
+    }
+    if lrs is not None:
+        errs["g_lrs"] = rel_l2(got["g_lrs"].cpu(), g_lrs)
+    bad = {k: e for k, e in errs.items() if not (e < _tol(k, theta_K, theta0))}
+    assert not bad, f"MAML {pde} W={W} L={L}: rel errors above {TOL}: {bad} (all: {errs})"
+    return errs
+
+
+def check_maml_adapt(K, pde, W, L, n, T, K_steps=3, inner_lr=1e-3, clip=1e14, seed=0):
+    out = PDE_OUT_DIM[pde]
+    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    inner, _, final, _, prm = make_maml_data(pde, n, n, T, K_steps, seed)
+    cfg = dict(inner_steps=K_steps, inner_lr=inner_lr, inner_grad_clip=clip, softplus_lrs=True, outer_loss_decay=0.0)
+    net = K.net_desc(L, W, out, OMEGA, True)
+    d = lambda sets: [_dev(K, s) for s in sets]
+    thf, losses = K.maml_adapt(net, pde, 1.0, cfg, _dev(K, theta0), None, [d(s) for s in inner], d(final), _dev(K, prm), T)
+    lf = oracle_loss_fn(pde, W, L, 1.0)
+    ocfg = ometa.MamlCfg(K_steps, inner_lr, clip, True, 0.0)
+    errs = {"theta": 0.0, "delta": 0.0, "losses": 0.0}
+    for t in range(T):
+        tk = ometa.MamlTask(oracle_params(pde, prm, t), [oracle_points(pde, s, t) for s in inner], None,
+                            oracle_points(pde, final, t), None)
+        th = theta0.double().requires_grad_(True)
+        thK, (_, ls), _ = ometa.maml_single_task_rollout(ocfg, lf, th, tk, None, with_outer=False, create_graph=False)
+        errs["theta"] = max(errs["theta"], rel_l2(thf[t].cpu(), thK.detach()))
+        errs["delta"] = max(errs["delta"], rel_l2(thf[t].cpu().double() - theta0.double(), thK.detach() - theta0.double()))
+        errs["losses"] = max(errs["losses"], rel_l2(losses[t].cpu(), ls.detach()))
+    bad = {k: e for k, e in errs.items() if not (e < TOL)}
+    assert not bad, f"MAML adapt {pde}: {bad} (all: {errs})"
+    return errs
+
+
+def check_leap(K, pde, W, L, n, T, K_steps=3, inner_lr=1e-3, clip=1e14, inner_opt="adam", seed=0):
+    out = PDE_OUT_DIM[pde]
+    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    sizes = synthetic.default_set_sizes(pde, n)
+    loss0, prm = synthetic.make_tasks(pde, T, sizes, seed=seed + 1)
+    step = [synthetic.make_tasks(pde, T, sizes, seed=seed + 20 + k)[0] for k in range(K_steps)]
+    new = [synthetic.make_tasks(pde, T, sizes, seed=seed + 40 + k)[0] for k in range(K_steps)]
+    cfg = dict(inner_steps=K_steps, inner_lr=inner_lr, inner_grad_clip=clip, norm=True, loss_in_distance=True,
+               stabilize=True, inner_opt=inner_opt, beta1=0.9, beta2=0.99, eps=1e-8)
+    net = K.net_desc(L, W, out, OMEGA, True)
+    d = lambda sets: [_dev(K, s) for s in sets]
+    got = K.leap_outer(net, pde, 1.0, cfg, _dev(K, theta0), d(loss0), [d(s) for s in step], [d(s) for s in new],
+                       _dev(K, prm), T, want_theta_final=True)
+    lf = oracle_loss_fn(pde, W, L, 1.0)
+    ocfg = ometa.LeapCfg(K_steps, inner_lr, clip, True, True, True, inner_opt)
+    tasks = [ometa.LeapTask(oracle_params(pde, prm, t), oracle_points(pde, loss0, t),
+                            [oracle_points(pde, s, t) for s in step], [oracle_points(pde, s, t) for s in new])
+             for t in range(T)]
+    outs = [ometa.leap_single_task_rollout(ocfg, lf, theta0.double(), tk) for tk in tasks]
+    mg = torch.stack([o[1] for o in outs]).mean(0)
+    losses = torch.stack([o[2] for o in outs])
+    thK = torch.stack([o[0] for o in outs])
+    errs = {
+        "meta_grad": rel_l2(got["meta_grad"].cpu(), mg),
+        "losses": rel_l2(got["losses"].cpu(), losses),
+        "theta_final": rel_l2(got["theta_final"].cpu(), thK),
+        "theta_delta": rel_l2(got["theta_final"].cpu().double() - theta0.double(), thK - theta0.double()),
+    }
+    bad = {k: e for k, e in errs.items() if not (e < _tol(k, thK, theta0))}
+    assert not bad, f"LEAP {pde} ({inner_opt}): {bad} (all: {errs})"
+    return errs
+
+
+def check_field_eval(K, W, L, out, n, T, seed=0):
+    theta = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta = torch.stack([theta * (1 + 0.05 * t) for t in range(T)])
+    coords = torch.rand(T, n, 2, generator=torch.Generator().manual_seed(seed + 3)) * 2 - 1
+    net = K.net_desc(L, W, out, OMEGA, True)
+    u = K.field_eval(net, _dev(K, theta), _dev(K, coords), T)
+    from oracle.field import nf_apply
+    for t in range(T):
+        params = unflatten_params(theta[t].double(), [W] * L, 2, out, True)
+        want = nf_apply(params, out, coords[t].double(), OMEGA)
+        e = rel_l2(u[t].cpu(), want)
+        assert e < TOL, f"field_eval W={W} out={out}: {e}"

@@ -1,0 +1,124 @@
+"""GPU parity tests proper: the CUDA kernels (through the C ABI, libmetapde_b200.so) against the float64
+oracle on the same seeded inputs, plus size-independent properties at BASELINE.json's full sizes."""
+import pytest
+import torch
+
+import parity_cases as pc
+from helpers import rel_l2, synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def test_native_library_is_cuda(gpu_kernels):
+    assert gpu_kernels.abi.backend() == "cuda"
+    assert gpu_kernels.abi.path.endswith("libmetapde_b200.so")
+
+
+@pytest.mark.parametrize("pde,W,L,n", [
+    ("poisson", 64, 3, 1024),            # C1 / C2 shape (README command)
+    ("td_burgers", 64, 3, 1024),         # C3 shape: sets 63 / 63 / 1010 / 1008
+    ("hyper_elasticity", 64, 3, 1024),   # C4 shape
+    ("poisson", 32, 2, 70),
+    ("poisson", 64, 1, 33),
+    ("poisson", 128, 2, 200),
+    ("poisson", 256, 5, 300),            # C5 network (5x256) at an oracle-sized point count
+    ("td_burgers", 256, 2, 100),
+    ("hyper_elasticity", 128, 4, 150),
+    ("td_burgers", 64, 8, 256),          # pipeline depth (pipleline_maml_meta.sh: 8x64)
+])
+def test_loss_grad_hvp(gpu_kernels, pde, W, L, n):
+    pc.check_loss_grad_hvp(gpu_kernels, pde, W, L, n, T=2)
+
+
+def test_many_tasks_shared_theta(gpu_kernels):
+    pc.check_loss_grad_hvp(gpu_kernels, "poisson", 64, 3, 100, T=8, bc_weight=100.0, per_task_theta=False)
+
+
+def test_single_point_sets(gpu_kernels):
+    # degenerate but legal: one point per set
+    pc.check_loss_grad_hvp(gpu_kernels, "poisson", 64, 2, 1, T=1, set_sizes=[1, 1])
+
+
+def test_field_eval(gpu_kernels):
+    pc.check_field_eval(gpu_kernels, 64, 3, 1, 1024, T=3)
+    pc.check_field_eval(gpu_kernels, 64, 3, 2, 1000, T=2)
+    pc.check_field_eval(gpu_kernels, 256, 5, 1, 777, T=1)
+
+
+@pytest.mark.parametrize("pde,W,L,n,lr", [
+    ("poisson", 64, 3, 256, 1e-2),
+    ("td_burgers", 64, 3, 256, 1e-2),
+    ("hyper_elasticity", 64, 3, 256, 1e-4),
+    ("poisson", 256, 2, 64, 1e-2),
+])
+def test_maml_outer(gpu_kernels, pde, W, L, n, lr):
+    pc.check_maml(gpu_kernels, pde, W, L, n, T=2, K_steps=2, inner_lr=lr)
+
+
+def test_maml_outer_clip_active_k5(gpu_kernels):
+    pc.check_maml(gpu_kernels, "poisson", 64, 3, 128, T=3, K_steps=5, inner_lr=1e-2, clip=1e-2, decay=0.1)
+
+
+def test_maml_outer_scalar_lr(gpu_kernels):
+    pc.check_maml(gpu_kernels, "poisson", 64, 2, 128, T=2, K_steps=2, inner_lr=1e-2, lr_tree=False)
+
+
+def test_maml_adapt(gpu_kernels):
+    pc.check_maml_adapt(gpu_kernels, "poisson", 64, 3, 256, T=2, K_steps=5, inner_lr=1e-2)
+
+
+@pytest.mark.parametrize("pde,opt", [("poisson", "adam"), ("poisson", "sgd"), ("td_burgers", "adam"), ("hyper_elasticity", "adam")])
+def test_leap_outer(gpu_kernels, pde, opt):
+    lr = {"adam": 1e-3, "sgd": 1e-2}[opt] * (1e-2 if pde == "hyper_elasticity" else 1.0)
+    pc.check_leap(gpu_kernels, pde, 64, 3, 256, T=2, K_steps=3, inner_lr=lr, inner_opt=opt)
+
+
+# ---------------------------------------------------------------------------------------------
+# full-size properties (C5: 5x256, 16384 boundary + 16384 domain points per task): no oracle at this size
+# ---------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def c5(gpu_kernels):
+    K = gpu_kernels
+    T, W, L, n = 2, 256, 5, 16384
+    theta = synthetic.siren_theta([W] * L, 1, 30.0, 30.0, True, seed=0).to(K.device)
+    sets, prm = synthetic.make_tasks("poisson", T, [n, n], seed=1)
+    sets = [s.to(K.device) for s in sets]
+    net = K.net_desc(L, W, 1, 30.0, True)
+    return K, net, theta, sets, prm.to(K.device), T
+
+
+def test_c5_hvp_linearity_and_symmetry(c5):
+    K, net, theta, sets, prm, T = c5
+    P = theta.numel()
+    g = torch.Generator().manual_seed(3)
+    v1 = torch.randn(T, P, generator=g).to(K.device)
+    v2 = torch.randn(T, P, generator=g).to(K.device)
+    _, _, g1, h1 = K.loss_hvp(net, "poisson", 1.0, theta, v1, sets, prm, T)
+    h1 = h1.clone(); g1 = g1.clone()
+    _, _, _, h2 = K.loss_hvp(net, "poisson", 1.0, theta, v2, sets, prm, T, want_grad=False)
+    h2 = h2.clone()
+    _, _, _, h12 = K.loss_hvp(net, "poisson", 1.0, theta, (0.5 * v1 - 2.0 * v2).contiguous(), sets, prm, T, want_grad=False)
+    assert rel_l2(h12.cpu(), (0.5 * h1 - 2.0 * h2).cpu()) < 1e-4          # linearity in v
+    for t in range(T):                                                       # symmetry of the Hessian
+        a = float((v1[t].double() * h2[t].double()).sum())
+        b = float((v2[t].double() * h1[t].double()).sum())
+        assert abs(a - b) <= 1e-3 * max(abs(a), abs(b)), (a, b)
+    # gradient from loss_grad == gradient from loss_hvp (different kernels)
+    _, _, g0 = K.loss_grad(net, "poisson", 1.0, theta, sets, prm, T)
+    assert rel_l2(g1.cpu(), g0.cpu()) < 1e-5
+
+
+def test_c5_directional_derivative(c5):
+    K, net, theta, sets, prm, T = c5
+    P = theta.numel()
+    loss, _, grad = K.loss_grad(net, "poisson", 1.0, theta, sets, prm, T)
+    loss = loss.clone(); grad = grad.clone()
+    d = grad[0] / grad[0].norm()
+    # central difference of the loss along the (normalised) gradient direction, float32-safe step
+    eps = 2e-3
+    lp, _ = K.loss(net, "poisson", 1.0, (theta + eps * d).contiguous(), sets, prm, T)
+    lp = lp.clone()
+    lm, _ = K.loss(net, "poisson", 1.0, (theta - eps * d).contiguous(), sets, prm, T)
+    fd = (lp[0].double() - lm[0].double()) / (2 * eps)
+    an = float((grad[0].double() * d.double()).sum())
+    assert abs(float(fd) - an) <= 2e-2 * abs(an), (float(fd), an)
