@@ -202,6 +202,14 @@ int mpde_leap_outer(const mpde_net_desc* net, const mpde_pde_desc* pde, const mp
 int64_t mpde_launch_count(void);
 /* "cuda" for the product build; the test-only emulator build answers "emu" */
 const char* mpde_backend(void);
+/* Optional device-side timing of the fused jet kernel (bench.py's roofline leg; the reference's
+ * counterpart is the wall-clock Timer around train_step, src/util/timer.py:5-27).  While enabled,
+ * every launch of the jet kernel is bracketed by a cudaEvent pair on the caller's stream (events
+ * are created on first use: do not enable inside a CUDA-graph capture).  mpde_prof_read
+ * synchronises on the recorded events of `mode` (mpde_mode), returns their summed duration in
+ * milliseconds and their count, and clears them. */
+int mpde_prof_enable(int on);
+int mpde_prof_read(int mode, double* total_ms, int64_t* launches);
 
 #ifdef __cplusplus
 }

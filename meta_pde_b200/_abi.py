@@ -92,6 +92,8 @@ SIGNATURES = {
                                   _P, C.c_size_t, _P]),
     "mpde_launch_count": (C.c_int64, []),
     "mpde_backend": (C.c_char_p, []),
+    "mpde_prof_enable": (C.c_int, [C.c_int]),
+    "mpde_prof_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }
 
 
@@ -283,6 +285,18 @@ class Kernels:
                                                     float(inner_lr), float(clip), _ptr(out), _ptr(gn), self._stream()))
         return out, gn
 
+    def prof_enable(self, on=True):
+        self._check(self.abi.mpde_prof_enable(int(bool(on))))
+
+    def prof_read(self, mode):
+        """-> (total_ms, launches) of the jet-kernel launches of ``mode`` since the last read."""
+        ms, n = C.c_double(0.0), C.c_int64(0)
+        self._check(self.abi.mpde_prof_read(int(mode), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def launch_count(self):
+        return int(self.abi.mpde_launch_count())
+
     def sumsq(self, x):
         out = torch.empty(1, dtype=torch.float32, device=self.device)
         nb = self.abi.mpde_sumsq_workspace_bytes(x.numel())
@@ -313,7 +327,7 @@ class Kernels:
         return arr, n_points
 
     def maml_outer(self, net, pde, bc_weight, cfg, theta0, inner_lrs, inner_sets, outer_sets, final_sets, aux_sets,
-                   pde_params, T, grad_scale=None, want_theta_final=False):
+                   pde_params, T, grad_scale=None, want_theta_final=False, out_g_theta=None, out_g_lrs=None):
         """cfg: dict(inner_steps, inner_lr, inner_grad_clip, softplus_lrs, outer_loss_decay).
         inner_sets / outer_sets: K lists of point tensors (ABI order); final_sets / aux_sets: one list each."""
         P = self.param_count(net)
@@ -333,8 +347,14 @@ class Kernels:
         lrs = self._t(inner_lrs, "inner_lrs")
         nt = len(PDE_TERMS[pde])
         dev = self.device
-        g_theta = torch.empty(P, dtype=torch.float32, device=dev)
-        g_lrs = torch.empty(K, P, dtype=torch.float32, device=dev) if lrs is not None else None
+        g_theta = self._t(out_g_theta, "out_g_theta") if out_g_theta is not None else torch.empty(P, dtype=torch.float32, device=dev)
+        if g_theta.numel() != P:
+            raise MpdeError(f"out_g_theta: expected {P} floats")
+        g_lrs = None
+        if lrs is not None:
+            g_lrs = self._t(out_g_lrs, "out_g_lrs") if out_g_lrs is not None else torch.empty(K, P, dtype=torch.float32, device=dev)
+            if g_lrs.numel() != K * P:
+                raise MpdeError(f"out_g_lrs: expected [{K}, {P}]")
         losses = torch.empty(T, K + 1, dtype=torch.float32, device=dev)
         meta = torch.empty(T, dtype=torch.float32, device=dev)
         aux = torch.empty(T, nt, dtype=torch.float32, device=dev)

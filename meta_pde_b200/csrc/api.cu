@@ -6,6 +6,7 @@
 #include "host_common.h"
 #include "aux_kernels.cuh"
 #include <mutex>
+#include <vector>
 
 namespace mpde {
 
@@ -26,6 +27,32 @@ int device_sm_count() {
   return n;
 #endif
 }
+
+// ---- optional event timing of the jet kernel (mpde_prof_enable / mpde_prof_read) ----
+#ifndef MPDE_EMU
+struct ProfState {
+  std::mutex mu;
+  bool on = false;
+  std::vector<cudaEvent_t> ev[3];   // pairs: [2i] start, [2i+1] stop
+  size_t used[3] = {0, 0, 0};
+};
+static ProfState g_prof;
+static bool prof_begin(int mode, void* stream, cudaEvent_t* stop) {
+  if (!g_prof.on) return false;
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  auto& v = g_prof.ev[mode];
+  if (g_prof.used[mode] + 2 > v.size()) {
+    cudaEvent_t a, b;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return false;
+    v.push_back(a); v.push_back(b);
+  }
+  cudaEvent_t start = v[g_prof.used[mode]];
+  *stop = v[g_prof.used[mode] + 1];
+  g_prof.used[mode] += 2;
+  cudaEventRecord(start, (cudaStream_t)stream);
+  return true;
+}
+#endif
 
 static int dispatch(int W, int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
   switch (W) {
@@ -225,7 +252,14 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   kp.scratch = scratch; kp.scratch_per_cta = (long long)pl.scratch_per_cta;
   kp.partial_g = pg; kp.partial_h = ph; kp.partial_terms = pt;
   kp.want_grad = want_grad;
+#ifndef MPDE_EMU
+  cudaEvent_t prof_stop;
+  const bool prof = prof_begin(mode, stream, &prof_stop);
+#endif
   rc = dispatch(pl.W, pl.pde, mode, 1, &kp, pl.G, T, stream, nullptr);
+#ifndef MPDE_EMU
+  if (prof) cudaEventRecord(prof_stop, (cudaStream_t)stream);
+#endif
   if (rc) return rc;
   // 3. loss terms
   {
@@ -299,6 +333,33 @@ const char* mpde_backend(void) {
 #else
   return "cuda";
 #endif
+}
+
+int mpde_prof_enable(int on) {
+#ifndef MPDE_EMU
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  g_prof.on = on != 0;
+  if (on) for (int m = 0; m < 3; ++m) g_prof.used[m] = 0;
+#else
+  (void)on;
+#endif
+  return MPDE_OK;
+}
+int mpde_prof_read(int mode, double* total_ms, int64_t* launches) {
+  if (mode < 0 || mode > 2 || !total_ms || !launches) return MPDE_INVALID_ARG;
+  *total_ms = 0.0; *launches = 0;
+#ifndef MPDE_EMU
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  auto& v = g_prof.ev[mode];
+  for (size_t i = 0; i + 1 < g_prof.used[mode]; i += 2) {
+    if (cudaEventSynchronize(v[i + 1]) != cudaSuccess) return MPDE_CUDA_ERROR;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, v[i], v[i + 1]) != cudaSuccess) return MPDE_CUDA_ERROR;
+    *total_ms += ms; *launches += 1;
+  }
+  g_prof.used[mode] = 0;
+#endif
+  return MPDE_OK;
 }
 
 size_t mpde_workspace_bytes(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, int mode) {

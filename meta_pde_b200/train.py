@@ -1,0 +1,193 @@
+"""Host-side mirror of the reference's jitted MAML / LEAP ``train_step`` for a flat theta.
+
+Reference (paths relative to /root/reference):
+  * MAML  ``train_step``   src/maml_pde.py:203-226  (multi_task_grad_and_losses, clip by the MODEL-grad norm,
+                           outer optimizer on theta, jax.experimental.optimizers.adam on the lr tree)
+  * LEAP  ``train_step``   src/leap_pde.py:175-195
+  * ``get_optimizer``      src/util/trainer_util.py:593-612 ("adam": Adam(b1 .9, b2 .99), "rmsprop": Adam(0, .8),
+                           "sgd": Momentum(beta 0); "ranger" is an un-pinned external package and is refused)
+
+Everything here is launch orchestration: the arithmetic runs in libmetapde_b200.so (the fused jet kernels and
+the parameter-sized kernels), the task mean across ranks is one NCCL all-reduce of the packed
+``[g_theta | g_lrs]`` buffer.  torch is used for device memory, streams and
+``torch.distributed`` only.  No CPU fallback: constructing a trainer without CUDA raises.
+"""
+import torch
+
+from . import ops
+from ._abi import PDE_NPRM, PDE_OUT_DIM, PDE_SETS, PDE_TERMS
+
+_ADAM_BETAS = {"adam": (0.9, 0.99), "rmsprop": (0.0, 0.8)}
+
+
+class MamlBatch:
+    """Pre-sampled points of ONE outer step for T tasks, packed in one flat float32 buffer.
+
+    Order of the (2K+2) point tuples: inner[0..K-1] (key k1 of scan step k, maml.py:134), outer[0..K-1] (k2),
+    final (final_key, maml.py:158), aux (outer_loss_key, maml.py:192); inside a tuple the ABI set order
+    (include/metapde_b200.h); each set is [T, n_s, 2].  ``pde_params`` is [T, nprm]."""
+
+    def __init__(self, pde, T, K, n_inner, n_outer, flat, pde_params):
+        self.pde, self.T, self.K = pde, int(T), int(K)
+        self.n_inner, self.n_outer = list(n_inner), list(n_outer)
+        self.flat, self.pde_params = flat, pde_params
+
+    @staticmethod
+    def numel(T, K, n_inner, n_outer):
+        return 2 * T * ((K + 1) * sum(n_inner) + (K + 1) * sum(n_outer))
+
+    @classmethod
+    def pack(cls, pde, K, inner, outer, final, aux, pde_params, pin=False):
+        """inner/outer: K lists of [T, n_s, 2] tensors; final/aux: one list each."""
+        T = inner[0][0].shape[0]
+        n_in = [s.shape[1] for s in inner[0]]
+        n_out = [s.shape[1] for s in outer[0]]
+        flat = torch.empty(cls.numel(T, K, n_in, n_out), dtype=torch.float32, pin_memory=pin)
+        off = 0
+        for sets in list(inner) + list(outer) + [final, aux]:
+            for s in sets:
+                n = s.numel()
+                flat[off:off + n] = s.reshape(-1)
+                off += n
+        assert off == flat.numel()
+        prm = pde_params.to(torch.float32).contiguous()
+        if pin:
+            prm = prm.pin_memory()
+        return cls(pde, T, K, n_in, n_out, flat, prm)
+
+    def to(self, device, out=None, non_blocking=True):
+        """Host -> device copy (into ``out``'s buffers when given); returns a device MamlBatch."""
+        if out is None:
+            out = MamlBatch(self.pde, self.T, self.K, self.n_inner, self.n_outer,
+                            torch.empty(self.flat.numel(), dtype=torch.float32, device=device),
+                            torch.empty(self.pde_params.shape, dtype=torch.float32, device=device))
+        out.flat.copy_(self.flat, non_blocking=non_blocking)
+        out.pde_params.copy_(self.pde_params, non_blocking=non_blocking)
+        return out
+
+    def nbytes(self):
+        return 4 * (self.flat.numel() + self.pde_params.numel())
+
+    def views(self):
+        """-> (inner [K][S], outer [K][S], final [S], aux [S]) as views of the flat buffer."""
+        T, K = self.T, self.K
+        off = 0
+        tuples = []
+        for sizes in [self.n_inner] * K + [self.n_outer] * K + [self.n_inner, self.n_outer]:
+            sets = []
+            for n in sizes:
+                sets.append(self.flat[off:off + 2 * T * n].view(T, n, 2))
+                off += 2 * T * n
+            tuples.append(sets)
+        return tuples[:K], tuples[K:2 * K], tuples[2 * K], tuples[2 * K + 1]
+
+
+class MamlTrainer:
+    """State + one outer step of MAML meta-training on this rank's share of the meta-batch.
+
+    ``train_step(step, batch)`` reproduces src/maml_pde.py:203-226 for the tasks in ``batch`` (the local
+    T_local = bsize / world_size tasks); with ``torch.distributed`` initialised the summed local gradients are
+    all-reduced (NCCL over NVLink) and scaled by 1/bsize, which is the reference's mean over the vmapped tasks
+    (src/nets/maml.py:231).  The clip + optimizer updates then run identically on every rank.
+    """
+
+    def __init__(self, pde, num_layers, layer_size, theta0, *, bsize, inner_steps, inner_lr, outer_lr, lr_inner_lr,
+                 siren_omega=30.0, log_scale=True, bc_weight=1.0, inner_grad_clip=1e14, grad_clip=1e14,
+                 outer_loss_decay=0.1, optimizer="adam", device=None, group=None):
+        self.K = ops.kernels(device)          # raises without CUDA / without the built library
+        self.device = self.K.device
+        self.pde = pde
+        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale)
+        self.P = self.K.param_count(self.net)
+        if theta0.numel() != self.P:
+            raise ValueError(f"theta0 has {theta0.numel()} parameters, the network needs {self.P}")
+        if optimizer not in ("adam", "rmsprop", "sgd"):
+            raise Exception("unknown optimizer: ", optimizer)   # trainer_util.py:610 (ranger: external, unpinned)
+        self.optimizer = optimizer
+        self.bsize, self.inner_steps = int(bsize), int(inner_steps)
+        self.cfg = dict(inner_steps=self.inner_steps, inner_lr=float(inner_lr), inner_grad_clip=float(inner_grad_clip),
+                        softplus_lrs=True, outer_loss_decay=float(outer_loss_decay))   # MamlDef, maml_pde.py:103-110
+        self.bc_weight, self.grad_clip = float(bc_weight), float(grad_clip)
+        self.outer_lr, self.lr_inner_lr = float(outer_lr), float(lr_inner_lr)
+        dev = self.device
+        self.theta = theta0.detach().to(dev, torch.float32).clone().contiguous()
+        self.inner_lrs = torch.ones(self.inner_steps, self.P, dtype=torch.float32, device=dev)   # maml_pde.py:151-154
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        self.m_theta, self.v_theta = z(self.P), z(self.P)
+        self.m_lrs, self.v_lrs = z(self.inner_steps, self.P), z(self.inner_steps, self.P)
+        self.t_theta = 0
+        self.group = group
+        self.world = torch.distributed.get_world_size(group) if torch.distributed.is_initialized() else 1
+        if self.bsize % self.world:
+            raise ValueError(f"bsize {self.bsize} must be a multiple of the world size {self.world}")
+        self.T_local = self.bsize // self.world
+        self._packed = torch.empty((self.inner_steps + 1) * self.P, dtype=torch.float32, device=dev)
+        self._dev_batch = None
+
+    # -- pieces (bench.py times them separately) ------------------------------------------------------------
+    def stage(self, host_batch):
+        """H2D copy of a pinned host batch into the trainer's persistent device staging buffers."""
+        self._dev_batch = host_batch.to(self.device, out=self._dev_batch)
+        return self._dev_batch
+
+    def meta_grad(self, batch):
+        """multi_task_grad_and_losses (maml.py:210-233) over the local tasks; returns the ABI result dict with
+        g_theta / g_lrs holding (1/bsize) * SUM over local tasks (all-reduced when distributed)."""
+        inner, outer, final, aux = batch.views()
+        P, K = self.P, self.inner_steps
+        out = self.K.maml_outer(self.net, self.pde, self.bc_weight, self.cfg, self.theta, self.inner_lrs, inner, outer,
+                                final, aux, batch.pde_params, batch.T, grad_scale=1.0 / self.bsize,
+                                out_g_theta=self._packed[:P], out_g_lrs=self._packed[P:].view(K, P))
+        if self.world > 1:
+            torch.distributed.all_reduce(self._packed, group=self.group)
+        return out
+
+    def apply(self, step, out):
+        """Clip by the model-grad norm (quirk: the lr-tree grads are rescaled by it too) + optimizer updates."""
+        K_ = self.K
+        g_theta, g_lrs = out["g_theta"], out["g_lrs"]
+        sumsq = K_.sumsq(g_theta)
+        self.t_theta += 1
+        if self.optimizer == "sgd":
+            K_.sgd_step(self.theta, g_theta, self.outer_lr, sumsq, self.grad_clip)
+        else:
+            b1, b2 = _ADAM_BETAS[self.optimizer]
+            K_.adam_step(self.theta, g_theta, self.m_theta, self.v_theta, self.t_theta, self.outer_lr, b1, b2, 1e-8,
+                         sumsq, self.grad_clip)
+        # jax.experimental.optimizers.adam(lr_inner_lr, b1=.9, b2=.99) at step index `step` (maml_pde.py:150,225)
+        K_.adam_step(self.inner_lrs.view(-1), g_lrs.reshape(-1), self.m_lrs.view(-1), self.v_lrs.view(-1), int(step) + 1,
+                     self.lr_inner_lr, 0.9, 0.99, 1e-8, sumsq, self.grad_clip)
+        return sumsq
+
+    def train_step(self, step, batch):
+        """One outer step on a DEVICE batch.  Returns (losses [T_local, K+1], meta_losses [T_local],
+        aux_terms [T_local, n_terms], meta_grad_norm [1]) as device tensors (no host sync)."""
+        out = self.meta_grad(batch)
+        sumsq = self.apply(step, out)
+        return out["losses"], out["meta_losses"], out["aux_terms"], torch.sqrt(sumsq)
+
+    def train_step_host(self, step, host_batch):
+        """The end-to-end call: pinned host batch in, host results out (H2D + step + D2H)."""
+        losses, meta, aux, gnorm = self.train_step(step, self.stage(host_batch))
+        res = torch.cat([losses.reshape(-1), meta.reshape(-1), aux.reshape(-1), gnorm.reshape(-1)]).cpu()
+        T, K = losses.shape[0], self.inner_steps
+        nt = len(PDE_TERMS[self.pde])
+        return (res[:T * (K + 1)].view(T, K + 1), res[T * (K + 1):T * (K + 2)],
+                res[T * (K + 2):T * (K + 2 + nt)].view(T, nt), res[-1])
+
+
+def synthetic_maml_batch(pde, T, K, n_inner, n_outer, seed, pin=False, task_offset=0):
+    """Seeded synthetic MamlBatch for tasks [task_offset, task_offset + T)."""
+    from . import synthetic
+
+    si, so = synthetic.default_set_sizes(pde, n_inner), synthetic.default_set_sizes(pde, n_outer)
+    base = int(seed) * 100003 + 7919 * int(task_offset)
+    inner, outer = [], []
+    _, prm = synthetic.make_tasks(pde, T, [1] * len(PDE_SETS[pde]), seed=base)
+    for k in range(K):
+        inner.append(synthetic.make_tasks(pde, T, si, seed=base + 10 * k + 1)[0])
+        outer.append(synthetic.make_tasks(pde, T, so, seed=base + 10 * k + 2)[0])
+    final = synthetic.make_tasks(pde, T, si, seed=base + 1001)[0]
+    aux = synthetic.make_tasks(pde, T, so, seed=base + 1002)[0]
+    assert prm.shape[1] == PDE_NPRM[pde]
+    return MamlBatch.pack(pde, K, inner, outer, final, aux, prm, pin=pin)
