@@ -1,0 +1,91 @@
+"""``python -m meta_pde_b200.compat.maml_pde`` -- drop-in for ``python -m src.maml_pde`` (src/maml_pde.py) on the
+hot path: same flags, same MamlDef / Field construction, same train_step semantics (src/maml_pde.py:203-226), NaN stop,
+text log and pickle checkpoints.  FEniCS validation and plots are out of scope."""
+import os
+
+import torch
+from absl import app
+
+from . import checkpoint, field, flags as cflags, maml, random as jr, trainer_util
+from .flags import FLAGS
+from .optim import Adam, Momentum
+from .pdes import get_pde
+from .tasks import make_task_loss_fns_factory
+from .. import ops
+
+cflags.define_maml()
+
+
+def build(pde):
+    """-> (maml_def, Field, optimizer, inner_lrs Model, lr-Adam state)  (src/maml_pde.py:100-159)"""
+    maml_def = maml.MamlDef(make_inner_opt=Momentum(learning_rate=FLAGS.inner_lr, beta=0.0).create,
+                            make_task_loss_fns=make_task_loss_fns_factory(pde), inner_steps=FLAGS.inner_steps,
+                            n_batch_tasks=FLAGS.bsize, softplus_lrs=True, outer_loss_decay=FLAGS.outer_loss_decay)
+    Field = pde.BaseField.partial(sizes=[FLAGS.layer_size for _ in range(FLAGS.num_layers)], dense_args=(),
+                                  nonlinearity=field.sin if FLAGS.siren else None, omega=FLAGS.siren_omega,
+                                  omega0=FLAGS.siren_omega0, log_scale=FLAGS.log_scale)
+    key, subkey = jr.split(jr.PRNGKey(0))
+    _, init_params = Field.init_by_shape(subkey, [((1, 2), "float32")])
+    model = field.Model(Field, init_params)
+    inner_lrs = field.Model(Field, torch.ones(FLAGS.inner_steps, model.theta.numel(), device=model.theta.device))
+    if FLAGS.load_model_from_expt is not None:
+        model, lrs = checkpoint.load(FLAGS.load_model_from_expt, Field)
+        inner_lrs = lrs if lrs is not None else inner_lrs
+    optimizer = trainer_util.get_optimizer(Field, model)
+    lr_state = {"m": torch.zeros_like(inner_lrs.theta), "v": torch.zeros_like(inner_lrs.theta)}
+    return key, maml_def, Field, optimizer, inner_lrs, lr_state
+
+
+def train_step(step, key, maml_def, optimizer, inner_lrs, lr_state):
+    """src/maml_pde.py:203-226.  Returns (optimizer, inner_lrs, losses, meta_losses, meta_grad_norm)."""
+    K = ops.kernels(optimizer.target.theta.device)
+    (g_model, g_lrs), losses, meta_losses = maml.multi_task_grad_and_losses(maml_def, key, optimizer.target, inner_lrs)
+    sumsq = K.sumsq(g_model.theta)                       # the norm of the MODEL grads only (quirk 1) ...
+    x = optimizer.target.theta.detach().clone()
+    od = optimizer.optimizer_def
+    if isinstance(od, Adam):
+        m, v, t = optimizer.state["m"].clone(), optimizer.state["v"].clone(), optimizer.state["step"] + 1
+        K.adam_step(x, g_model.theta, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, sumsq, FLAGS.grad_clip)
+        state = {"step": t, "m": m, "v": v}
+    else:
+        K.sgd_step(x, g_model.theta, od.learning_rate, sumsq, FLAGS.grad_clip)
+        state = {"step": optimizer.state["step"] + 1}
+    optimizer = type(optimizer)(od, field.Model(optimizer.target.module, x), state)
+    lrs = inner_lrs.theta.detach().clone()               # ... rescales the lr-tree grads too; jax adam at index `step`
+    K.adam_step(lrs.view(-1), g_lrs.theta.contiguous().view(-1), lr_state["m"].view(-1), lr_state["v"].view(-1), step + 1,
+                FLAGS.lr_inner_lr, 0.9, 0.99, 1e-8, sumsq, FLAGS.grad_clip)
+    return optimizer, field.Model(inner_lrs.module, lrs), losses, meta_losses, torch.sqrt(sumsq)
+
+
+def main(argv):
+    if FLAGS.out_dir is None:
+        FLAGS.out_dir = FLAGS.pde + "_maml_results"
+    pde = get_pde(FLAGS.pde)
+    path, log, _ = trainer_util.prepare_logging(FLAGS.out_dir, FLAGS.expt_name)
+    log(FLAGS.flags_into_string())
+    with open(os.path.join(path, "flags_config.txt"), "w") as f:
+        f.write(FLAGS.flags_into_string())
+    key, maml_def, Field, optimizer, inner_lrs, lr_state = build(pde)
+    log("NN model:", {k: (tuple(v.shape) if torch.is_tensor(v) else {kk: tuple(vv.shape) for kk, vv in v.items()})
+                      for k, v in optimizer.target.params.items()})
+    for step in range(FLAGS.outer_steps):
+        key, subkey = jr.split(key, 2)
+        with trainer_util.Timer() as t:
+            optimizer, inner_lrs, losses, meta_losses, meta_grad_norm = train_step(step, subkey, maml_def, optimizer,
+                                                                                    inner_lrs, lr_state)
+        if FLAGS.measure_grad_norm_every > 0 and step % FLAGS.measure_grad_norm_every == 0:
+            log("loss vals and grad norms: ", {k: float(v.sum()) for k, v in meta_losses[1].items()})
+            log("meta grad norm: ", float(meta_grad_norm))
+        if bool(torch.isnan(meta_losses[0].mean())):
+            log("encountered nan at at step {}".format(step))
+            break
+        if step % FLAGS.log_every == 0:
+            log("step: {}, meta_loss: {}, losses: {}, meta_grad_norm: {}, per train step time: {}".format(
+                step, float(meta_losses[0].mean()), losses.mean(dim=0).tolist(), float(meta_grad_norm), t.interval))
+        if FLAGS.viz_every > 0 and step % FLAGS.viz_every == 0:
+            checkpoint.save(path, step, optimizer.target, inner_lrs)
+    return optimizer, inner_lrs
+
+
+if __name__ == "__main__":
+    app.run(main)

@@ -1,0 +1,195 @@
+"""CPU tests of the host-side mirror of the reference's plugin surface (meta_pde_b200/compat): PRNG golden vectors,
+flags, samplers, SIREN init, checkpoint layout, the no-fallback rule, and the task-sharding logic over gloo."""
+import math
+import os
+import pickle
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from meta_pde_b200.compat import flags as cflags
+
+cflags.define_maml()
+cflags.ensure_parsed(["test"])
+from meta_pde_b200.compat import checkpoint, field, pdes, random as jr  # noqa: E402
+from meta_pde_b200.compat.flags import FLAGS  # noqa: E402
+
+
+def test_prng_golden_vectors():
+    """The only golden vectors of the reference: src/.ipynb_checkpoints/Untitled-checkpoint.ipynb:183,215,236,257-259."""
+    assert jr.split(jr.PRNGKey(0), 3).tolist() == [[2467461003, 428148500], [3186719485, 3840466878], [2562233961, 1946702221]]
+    # the notebook shows numpy's 8-digit array print of the float32 values
+    assert np.array2string(jr.uniform(jr.PRNGKey(0), (1,), minval=0, maxval=0.1)) == "[0.04184571]"
+    assert np.array2string(jr.uniform(jr.PRNGKey(0), (1,), minval=0, maxval=0.12)) == "[0.05021484]"
+
+
+def test_prng_streams_are_well_formed():
+    u = jr.uniform(jr.PRNGKey(7), (4097,))             # odd size: the zero-padded counter path
+    assert u.dtype == np.float32 and 0.0 <= u.min() and u.max() < 1.0 and abs(u.mean() - 0.5) < 0.02
+    n = jr.normal(jr.PRNGKey(8), (20000,))
+    assert abs(n.mean()) < 0.03 and abs(n.std() - 1.0) < 0.03
+    idx = jr.choice_without_replacement(jr.PRNGKey(9), 100, 30, np.r_[np.ones(50), np.zeros(50)])
+    assert len(set(idx.tolist())) == 30 and idx.max() < 50      # zero-probability entries are never drawn
+
+
+def test_flag_defaults_match_reference():
+    # src/util/common_flags.py:14-15,59-62,78-86 and src/maml_pde.py:50-58
+    assert (FLAGS.bc_weight, FLAGS.xmin, FLAGS.xmax, FLAGS.ymin, FLAGS.ymax) == (100.0, 0.0, 1.0, -1.0, 1.0)
+    assert (FLAGS.num_layers, FLAGS.layer_size, FLAGS.siren_omega, FLAGS.siren_omega0) == (3, 64, 1.0, 3.0)
+    assert (FLAGS.bsize, FLAGS.inner_steps, FLAGS.inner_lr, FLAGS.outer_loss_decay, FLAGS.inner_grad_clip) == (16, 5, 3e-5, 0.1, 1e14)
+    assert FLAGS.optimizer == "ranger" and FLAGS.log_scale and FLAGS.siren
+
+
+def test_get_pde_registry():
+    assert pdes.get_pde("poisson").BaseField is field.NeuralPotential and FLAGS.domain_loss == "domain_loss"
+    assert pdes.get_pde("hyper_elasticity").dim == 3
+    with pytest.raises(Exception, match="Invalid PDE"):
+        pdes.get_pde("stokes")
+
+
+@pytest.mark.parametrize("name,n,shapes", [
+    ("poisson", 128, [(128, 2), (128, 2)]),
+    ("td_burgers", 1024, [(63, 2), (63, 2), (1010, 2), (1008, 2)]),
+])
+def test_sampler_shapes_and_geometry(name, n, shapes):
+    p = pdes.get_pde(name)
+    prm = p.sample_params(jr.PRNGKey(1))
+    pts = p.sample_points(jr.PRNGKey(2), n, prm)
+    assert [tuple(x.shape) for x in pts] == shapes
+    again = p.sample_points(jr.PRNGKey(2), n, prm)
+    assert all(torch.equal(a, b) for a, b in zip(pts, again))              # keyed: deterministic
+    if name == "poisson":
+        c1, c2 = prm[2].tolist()
+        th = torch.atan2(pts[0][:, 1], pts[0][:, 0])
+        r0 = 1 + c1 * torch.cos(4 * th) + c2 * torch.cos(8 * th)
+        assert torch.allclose(pts[0].norm(dim=1), r0, atol=1e-5)           # boundary points lie on r0(theta)
+        assert float(pts[1][:, 0].min()) >= FLAGS.xmin                      # default xmin = 0 (quirk 9)
+    else:
+        assert torch.equal(pts[0][:, 1], pts[1][:, 1])                      # left / right share their times (quirk 7)
+        assert float(pts[2][:, 1].abs().max()) == 0.0
+
+
+def test_hyper_sampler():
+    FLAGS.max_holes = 5
+    try:
+        p = pdes.get_pde("hyper_elasticity")
+        prm = p.sample_params(jr.PRNGKey(3))
+        assert tuple(prm[2].shape) == (25, 5) and prm[3] == 25
+        pts = p.sample_points(jr.PRNGKey(4), 64, prm)
+        assert len(pts) == 6 and all(tuple(x.shape) == (64, 2) for x in pts)
+        assert float((pts[0][:, 1] - FLAGS.ymax).abs().max()) == 0.0 and float((pts[1][:, 1] - FLAGS.ymin).abs().max()) == 0.0
+        inh = p._in_hole(pts[5].numpy(), prm[2].numpy(), 25)
+        assert not inh.any()                                                # domain points avoid the pores
+        assert len(p.abi_sets(pts)) == 3
+    finally:
+        FLAGS.max_holes = 12
+
+
+def test_siren_init_and_param_tree():
+    Field = field.NeuralPotential.partial(sizes=[64, 64, 64], dense_args=(), nonlinearity=field.sin, omega=30.0, omega0=30.0,
+                                          log_scale=True)
+    _, params = Field.init_by_shape(jr.PRNGKey(0), [((1, 2), "float32")])
+    assert list(params) == ["Dense_0", "Dense_1", "Dense_2", "Dense_3", "log_input_scale", "log_output_scale"]
+    assert tuple(params["Dense_0"]["kernel"].shape) == (2, 64) and tuple(params["Dense_3"]["kernel"].shape) == (64, 1)
+    assert tuple(params["log_input_scale"].shape) == (1, 2)
+    assert float(params["Dense_0"]["kernel"].abs().max()) <= 0.5                       # (omega0/omega) U(+-1/fan_in)
+    assert float(params["Dense_1"]["kernel"].abs().max()) <= math.sqrt(6 / 64) / 30    # U(+-sqrt(6/fan_in)/omega)
+    assert float(params["Dense_1"]["bias"].abs().max()) == 0.0
+    assert abs(float(params["log_output_scale"][0, 0]) - math.log(0.1)) < 1e-6
+    m = field.Model(Field, params)
+    assert m.theta.numel() == 8580                                                     # P at 3x64
+    with pytest.raises(NotImplementedError):
+        field.NeuralPotential.partial(sizes=[64], nonlinearity=None).spec()            # --nosiren: unsupported, no fallback
+
+
+def test_checkpoint_layout_roundtrip(tmp_path):
+    Field = field.make_nf_ndim(2).partial(sizes=[32, 32], nonlinearity=field.sin, omega=30.0, omega0=30.0, log_scale=True)
+    _, params = Field.init_by_shape(jr.PRNGKey(5), [((1, 2), "float32")])
+    model = field.Model(Field, params)
+    lrs = field.Model(Field, torch.ones(5, model.theta.numel()))
+    fn = checkpoint.save(str(tmp_path), 300, model, lrs)
+    checkpoint.save(str(tmp_path), 20, model, lrs)
+    obj = pickle.load(open(fn, "rb"))
+    assert isinstance(obj, list) and set(obj[0]) == {"params"}                          # [model_state, lrs_state]
+    assert obj[0]["params"]["Dense_2"]["kernel"].shape == (32, 2) and obj[1]["params"]["Dense_0"]["kernel"].shape == (5, 2, 32)
+    assert checkpoint.latest(str(tmp_path)).endswith("model_step_300.pickle")           # highest step wins
+    m2, l2 = checkpoint.load(str(tmp_path), Field)
+    assert torch.equal(m2.theta.cpu(), model.theta.cpu()) and torch.equal(l2.theta.cpu(), lrs.theta.cpu())
+
+
+def test_no_cpu_fallback():
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    from meta_pde_b200 import ops
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.kernels()
+    Field = field.NeuralPotential.partial(sizes=[32], nonlinearity=field.sin, omega=30.0, omega0=30.0, log_scale=True)
+    _, params = Field.init_by_shape(jr.PRNGKey(0), [((1, 2), "float32")])
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        field.Model(Field, params)(torch.zeros(3, 2))
+
+
+def test_abi_library_exports_every_symbol():
+    from meta_pde_b200 import ops
+    from meta_pde_b200._abi import SIGNATURES
+    import re
+    a = ops.abi()
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "metapde_b200.h")).read()
+    declared = set(re.findall(r"\b(mpde_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(SIGNATURES), declared ^ set(SIGNATURES)
+    for name in declared:
+        assert hasattr(a, name)
+    assert a.backend() == "cuda" and a.mpde_num_terms(1) == 4 and a.mpde_num_pde_params(0) == 13
+
+
+# ------------------------------------------------------------------------------------------------ gloo, world size 2
+def _shard_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch.distributed as dist
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path[:0] = [root, os.path.join(root, "tests")]
+    from meta_pde_b200 import ops, synthetic, train
+    from meta_pde_b200._abi import Abi, Kernels
+    emu = Kernels(Abi(os.path.join(root, "tests", "emu", "libmetapde_emu.so")), "cpu")
+    ops.kernels = lambda device=None: emu                      # TEST ONLY: host logic over the emulator build
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    T, K, W, L, n = 4, 2, 32, 2, 24
+    theta0 = synthetic.siren_theta([W] * L, 1, 30.0, 30.0, True, seed=0, bias_scale=0.05)
+    tr = train.MamlTrainer("poisson", L, W, theta0, bsize=T, inner_steps=K, inner_lr=1e-2, outer_lr=1e-3, lr_inner_lr=0.5,
+                           device="cpu")
+    assert tr.T_local == T // world
+    batch = train.synthetic_maml_batch("poisson", tr.T_local, K, n, n, seed=3, task_offset=rank * tr.T_local)
+    losses, meta, aux, gnorm = tr.train_step(0, batch)
+    torch.save({"theta": tr.theta, "lrs": tr.inner_lrs, "packed": tr._packed, "gnorm": gnorm}, os.path.join(out_dir, f"r{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_task_sharding_world2_matches_single(tmp_path, emu_kernels):
+    import torch.multiprocessing as mp
+    from meta_pde_b200 import ops, synthetic, train
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_shard_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (torch.load(os.path.join(str(tmp_path), f"r{r}.pt")) for r in (0, 1))
+    for k in ("theta", "lrs", "packed"):
+        assert torch.equal(r0[k], r1[k]), k                     # ranks stay replicated after the all-reduced update
+    # single process over the same 4 tasks
+    saved = ops.kernels
+    ops.kernels = lambda device=None: emu_kernels
+    try:
+        T, K, W, L, n = 4, 2, 32, 2, 24
+        theta0 = synthetic.siren_theta([W] * L, 1, 30.0, 30.0, True, seed=0, bias_scale=0.05)
+        tr = train.MamlTrainer("poisson", L, W, theta0, bsize=T, inner_steps=K, inner_lr=1e-2, outer_lr=1e-3, lr_inner_lr=0.5,
+                               device="cpu")
+        halves = [train.synthetic_maml_batch("poisson", 2, K, n, n, seed=3, task_offset=o) for o in (0, 2)]
+        inner, outer, final, aux = zip(*[b.views() for b in halves])
+        cat = lambda parts: [torch.cat([p[s] for p in parts]) for s in range(len(parts[0]))]
+        full = train.MamlBatch.pack("poisson", K, [cat([i[k] for i in inner]) for k in range(K)],
+                                    [cat([o[k] for o in outer]) for k in range(K)], cat(final), cat(aux),
+                                    torch.cat([b.pde_params for b in halves]))
+        tr.train_step(0, full)
+    finally:
+        ops.kernels = saved
+    assert torch.allclose(tr._packed, r0["packed"], rtol=1e-5, atol=1e-9)      # mean over tasks: same up to summation order
+    assert torch.allclose(tr.theta, r0["theta"], rtol=1e-5, atol=1e-7)
