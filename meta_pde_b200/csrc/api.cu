@@ -5,6 +5,10 @@
 #include "../../include/metapde_b200.h"
 #include "host_common.h"
 #include "aux_kernels.cuh"
+#ifndef MPDE_EMU
+#include "tc_params.cuh"
+#endif
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -64,6 +68,17 @@ static int dispatch(int W, int pde, int mode, int op, const KParams* p, int gx, 
   return MPDE_UNSUPPORTED_NET;
 }
 
+// The tensor-core path serves widths 128/256 where it is implemented; MPDE_DISABLE_TC=1 forces the FP32-FMA kernels.
+static bool use_tc_path(int W, int L, int mode) {
+#ifdef MPDE_EMU
+  (void)W; (void)L; (void)mode;
+  return false;
+#else
+  static const bool disabled = []() { const char* e = getenv("MPDE_DISABLE_TC"); return e && e[0] == '1'; }();
+  return !disabled && tc_supported(W, L, mode);
+#endif
+}
+
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 struct Carver {
@@ -106,6 +121,8 @@ struct EvalPlan {
   size_t scratch_per_cta;   // floats
   // workspace sizes (floats)
   size_t n_th, n_thd, n_scratch, n_pg, n_ph, n_pt, n_gtmp;
+  bool tc;                  // tensor-core path
+  size_t n_wimg, n_wshift;  // floats: tc weight image [T][image], shifts [T][16]
   size_t bytes;
 };
 
@@ -140,6 +157,11 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
     pl->term_scale[0] = 1000.f; pl->term_scale[1] = 1000.f; pl->term_scale[2] = 1.f;
     pl->weight[0] = bw; pl->weight[1] = bw; pl->weight[2] = 1.f;
   }
+  pl->tc = use_tc_path(pl->W, pl->L, mode);
+#ifndef MPDE_EMU
+  if (pl->tc) rc = dispatch_tc(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
+  else
+#endif
   rc = dispatch(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
   if (rc) return rc;
   const int NP = pl->ki.np;
@@ -178,8 +200,13 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   pl->n_ph = (mode == MODE_HVP) ? ctas * pl->P : 0;
   pl->n_pt = ctas * MAX_SEG;
   pl->n_gtmp = need_gtmp ? (size_t)T * pl->P : 0;
+  pl->n_wimg = 0; pl->n_wshift = 0;
+#ifndef MPDE_EMU
+  if (pl->tc) { pl->n_wimg = (size_t)T * (tc_image_bytes(pl->W, pl->L) / 4); pl->n_wshift = (size_t)T * tc::TC_MAX_L * 2; }
+#endif
   Carver c(nullptr, 0);
   c.take(pl->n_th); c.take(pl->n_thd); c.take(pl->n_scratch); c.take(pl->n_pg); c.take(pl->n_ph); c.take(pl->n_pt); c.take(pl->n_gtmp);
+  c.take(pl->n_wimg); c.take(pl->n_wshift);
   pl->bytes = c.off + 256;
   return MPDE_OK;
 }
@@ -218,6 +245,8 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   Carver c(wsb, ws_bytes);
   float* th = c.take(pl.n_th); float* thd = c.take(pl.n_thd); float* scratch = c.take(pl.n_scratch);
   float* pg = c.take(pl.n_pg); float* ph = c.take(pl.n_ph); float* pt = c.take(pl.n_pt); float* gtmp = c.take(pl.n_gtmp);
+  float* wimg = c.take(pl.n_wimg); float* wshift = c.take(pl.n_wshift);
+  (void)wimg; (void)wshift;
   if (mode != MODE_HVP) thd = nullptr;
 
   // 1. prep: theta -> theta-hat (shared theta: prepared once)
@@ -253,8 +282,24 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   kp.partial_g = pg; kp.partial_h = ph; kp.partial_terms = pt;
   kp.want_grad = want_grad;
 #ifndef MPDE_EMU
+  if (pl.tc) {
+    // weight image for the tensor-core kernels (hidden kernels from natural theta, output layer from theta-hat)
+    rc = tc_launch_prep(pl.W, pl.L, pl.OUT, T_prep, theta, theta_stride, th, kp.th_stride, (uint8_t*)wimg,
+                        (long long)tc_image_bytes(pl.W, pl.L), (int*)wshift, 2 * tc::TC_MAX_L, stream);
+    if (rc) return rc;
+  }
   cudaEvent_t prof_stop;
   const bool prof = prof_begin(mode, stream, &prof_stop);
+#endif
+#ifndef MPDE_EMU
+  if (pl.tc) {
+    const long long img_bytes = (long long)tc_image_bytes(pl.W, pl.L);
+    tc::TcParams tp;
+    tp.k = kp;
+    tp.wimg = (const uint8_t*)wimg; tp.wimg_stride = (T_prep == 1) ? 0 : img_bytes;
+    tp.wshift = (const int*)wshift; tp.wshift_stride = (T_prep == 1) ? 0 : 2 * tc::TC_MAX_L;
+    rc = dispatch_tc(pl.W, pl.pde, mode, 1, &tp, pl.G, T, stream, nullptr);
+  } else
 #endif
   rc = dispatch(pl.W, pl.pde, mode, 1, &kp, pl.G, T, stream, nullptr);
 #ifndef MPDE_EMU

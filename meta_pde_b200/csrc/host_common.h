@@ -22,6 +22,17 @@ int dispatch_w64(int pde, int mode, int op, const KParams* p, int gx, int gy, vo
 int dispatch_w128(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
 int dispatch_w256(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
 
+// tensor-core (tcgen05) path, widths 128 / 256 (tc_inst.cu; not part of the emulator build)
+#ifndef MPDE_EMU
+namespace tc { struct TcParams; }
+bool tc_supported(int W, int L, int mode);
+int dispatch_tc(int W, int pde, int mode, int op, const tc::TcParams* p, int gx, int gy, void* stream, KernelInfo* info);
+size_t tc_image_bytes(int W, int L);
+int tc_launch_prep(int W, int L, int OUT, int T, const float* theta, long long theta_stride, const float* th,
+                   long long th_stride, uint8_t* wimg, long long wimg_stride, int* wshift, long long wshift_stride,
+                   void* stream);
+#endif
+
 #ifdef MPDE_EMU
 #define MPDE_LAUNCH(kfn, grid, block, smem, stream, ...)                                   \
   do { ::mpde::g_launches++; emu::launch(grid, block, smem, [=]() { kfn(__VA_ARGS__); }); } while (0)

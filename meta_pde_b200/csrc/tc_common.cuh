@@ -9,6 +9,7 @@
 // (rows = K index, the 128 B run along M/N).
 #pragma once
 #include <cstdint>
+#include <cstdio>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 

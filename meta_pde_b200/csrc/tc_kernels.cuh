@@ -1,0 +1,501 @@
+// tc_kernels.cuh -- tensor-core (tcgen05 / TMEM) path of the fused SIREN jet kernels for layer widths 128 and 256.
+//
+// Same math as pde_kernels.cuh (reference: src/nets/field.py:47-72,146-199 and the three loss_fn, see there), but the
+// per-layer [jet rows x W] x [W x W] contractions run on the 5th-generation tensor cores in split precision:
+// every fp32 operand x is carried as fp16 (hi, lo) with hi + lo = x * 2^shift to 22 bits, and a product is the three
+// kind::f16 MMAs hi*hi + lo*hi + hi*lo accumulated in fp32 in tensor memory (measured 7e-7 rel-L2 on B200,
+// profiles/r01_tc_probe.jsonl).  Block scaling: one power-of-two shift per (tile, layer, jet channel) for the
+// activations (from an exact-or-upper bound of the channel maximum, so nothing overflows fp16) and one per layer
+// for the weights.
+//
+// Orientation ("transposed"): D[neuron][row] = sum_k Wt[neuron][k] * X[row][k].  The weights are the A operand
+// (M = 128 neurons per MMA, streamed from L2 through a bulk-copy ring, pre-swizzled by tc_prep_kernel), the tile's
+// jet rows are the B operand (N = 128 rows resident in shared memory), and a TMEM lane is a neuron: the epilogue
+// thread of neuron n reads its accumulator row with tcgen05.ld and has all jet channels of every point of the tile
+// in registers, so the sin-jet algebra is thread-local exactly as in the FP32-FMA kernel.
+//
+// Warp roles per CTA: W/32 epilogue warps (thread = neuron), one bulk-copy producer warp, one MMA-issuer warp.
+#pragma once
+#include "compat.cuh"
+#include "jet_math.cuh"
+#include "pde_kernels.cuh"
+#include "tc_common.cuh"
+#include "tc_params.cuh"
+
+namespace mpde {
+namespace tc {
+
+constexpr int TR = 128;                 // jet rows per tile (MMA N)
+constexpr int STAGE_BYTES = 32768;      // one ring stage: [128 neurons][64 k] fp16 hi (16 KB) then lo (16 KB)
+constexpr int NSTAGE = 3;
+
+template <int W> struct TcGeo {
+  static constexpr int NMT = W / 128;                 // M tiles (128 neurons each)
+  static constexpr int KSL = W / 64;                  // 64-wide k slabs
+  static constexpr int NEPI = W;                      // epilogue threads
+  static constexpr int NT = W + 64;                   // + producer warp + MMA warp
+  static constexpr int SLAB = TR * 128;               // bytes of one [128 rows][64 k] fp16 slab
+  static constexpr int XBYTES = 2 * KSL * SLAB;       // hi slabs then lo slabs
+  static constexpr int RING = NSTAGE * STAGE_BYTES;
+  // misc (bytes): xs[2][TR] f32, ybuf[TR][2] f32, red[TR] f32, cmax[2][4] u32, shifts[TC_MAX_L][4] i32, terms[4] f32,
+  //               barriers (2*NSTAGE + 3) u64, tmem slot u32
+  static constexpr int MISC = 2 * TR * 4 + 2 * TR * 4 + TR * 4 + 32 + TC_MAX_L * 16 + 16 + (2 * NSTAGE + 3) * 8 + 16;
+  static constexpr int SMEM = XBYTES + RING + MISC;
+  static constexpr int TMEM_COLS = NMT * TR;          // 128 or 256 (power of two)
+  // global weight image per task: hidden layers 1..L-1 (forward copy: NMT*KSL stages each), then the output layer
+  static constexpr size_t layer_bytes() { return (size_t)NMT * KSL * STAGE_BYTES; }
+  static constexpr size_t out_bytes() { return (size_t)KSL * STAGE_BYTES; }
+  static size_t image_bytes(int L) { return (size_t)(L - 1) * layer_bytes() + out_bytes(); }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// tc_prep_kernel: natural theta (hidden kernels [n_in][n_out]) + theta-hat (output layer) -> swizzled fp16 hi/lo
+// stages in streaming order.  grid (stages_per_task, T), 256 threads.  Each block recomputes its layer's max.
+// ---------------------------------------------------------------------------------------------------------
+struct TcPrepParams {
+  int W, L, OUT, T;
+  const float* theta; long long theta_stride;   // natural parameters (or the HVP direction)
+  const float* th;    long long th_stride;      // theta-hat (effective output layer wLe [W][OUT])
+  uint8_t* wimg; long long wimg_stride;
+  int* wshift; long long wshift_stride;
+};
+
+// shift s with max * 2^s in [2^13, 2^14); 0 for an all-zero block
+TC_DEV int shift_for_max(float mx, int target = 14) {
+  if (!(mx > 0.f)) return 0;
+  const int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;   // mx < 2^e
+  int s = target - e;
+  s = s < -100 ? -100 : (s > 100 ? 100 : s);
+  return s;
+}
+TC_DEV float pow2i(int s) { return __uint_as_float((uint32_t)(s + 127) << 23); }
+
+__global__ void __launch_bounds__(256) tc_prep_kernel(TcPrepParams p) {
+  const int W = p.W, L = p.L, OUT = p.OUT;
+  const int NMT = W / 128, KSL = W / 64;
+  const int t = blockIdx.y;
+  const int st = blockIdx.x;                          // stage index inside the task image
+  const int per_layer = NMT * KSL;
+  const bool is_out = st >= (L - 1) * per_layer;
+  const int l = is_out ? L : 1 + st / per_layer;      // step index (hidden layer l, or L = output layer)
+  const int rem = is_out ? st - (L - 1) * per_layer : st % per_layer;
+  const int mt = is_out ? 0 : rem / KSL, s = is_out ? rem : rem % KSL;
+  const float* src = is_out ? p.th + (size_t)t * p.th_stride + ph_off_out(W, L)
+                            : p.theta + (size_t)t * p.theta_stride + nat_off_layer(W, l);
+  const int count = is_out ? W * OUT : W * W;
+  __shared__ float red[256];
+  float mx = 0.f;
+  for (int i = threadIdx.x; i < count; i += 256) mx = fmaxf(mx, fabsf(src[i]));
+  red[threadIdx.x] = mx;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] = fmaxf(red[threadIdx.x], red[threadIdx.x + o]);
+    __syncthreads();
+  }
+  const int sh = shift_for_max(red[0]);
+  const float sc = pow2i(sh);
+  if (rem == 0 && threadIdx.x == 0) p.wshift[(size_t)t * p.wshift_stride + l] = sh;
+  uint8_t* dst = p.wimg + (size_t)t * p.wimg_stride + (size_t)st * STAGE_BYTES;
+  for (int i = threadIdx.x; i < 128 * 64; i += 256) {
+    const int m = i >> 6, kk = i & 63;
+    const int n = mt * 128 + m, k = s * 64 + kk;
+    float w;
+    if (is_out) w = (m < OUT) ? src[k * OUT + m] : 0.f;
+    else w = src[(size_t)k * W + n];
+    __half h, lo;
+    split_f16(w * sc, h, lo);
+    const uint32_t off = sw128_off(m, kk * 2);
+    *reinterpret_cast<__half*>(dst + off) = h;
+    *reinterpret_cast<__half*>(dst + 16384 + off) = lo;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// shared-memory carve-up and per-CTA context
+// ---------------------------------------------------------------------------------------------------------
+extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
+
+template <int W> struct TcCtx {
+  typedef TcGeo<W> G;
+  uint8_t* xbuf; uint8_t* ring;
+  float* xs; float* ybuf; float* red; uint32_t* cmax; int* shifts; float* terms;
+  uint64_t* full; uint64_t* empty; uint64_t* xready; uint64_t* dfull;
+  uint32_t* tmem_slot;
+  TC_DEV void carve() {
+    uint8_t* s = tc_smem_raw;
+    xbuf = s; ring = s + G::XBYTES;
+    xs = reinterpret_cast<float*>(ring + G::RING);
+    ybuf = xs + 2 * TR; red = ybuf + 2 * TR;
+    cmax = reinterpret_cast<uint32_t*>(red + TR);
+    shifts = reinterpret_cast<int*>(cmax + 8);
+    terms = reinterpret_cast<float*>(shifts + TC_MAX_L * 4);
+    full = reinterpret_cast<uint64_t*>(terms + 4);
+    empty = full + NSTAGE; xready = empty + NSTAGE; dfull = xready + 1;
+    tmem_slot = reinterpret_cast<uint32_t*>(dfull + 2);
+  }
+};
+
+// barrier among the epilogue warps only (named barrier 1)
+template <int NEPI> TC_DEV void epi_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NEPI) : "memory"); }
+
+// warp max of non-negative floats (uint order == float order), folded into shared cmax[c]
+TC_DEV void fold_max(uint32_t* slot, float v, int lane) {
+  const uint32_t m = __reduce_max_sync(0xffffffffu, __float_as_uint(v));
+  if (lane == 0 && m != 0u) atomicMax(slot, m);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Per-tile epilogue work of one epilogue thread (= neuron n).  HEAD selects jet kind / channel count.
+// Row r of the tile: channel sets r = 4 * point + channel (32 points, 3-channel jets padded to 4 rows);
+// value sets r = point (128 points).
+// ---------------------------------------------------------------------------------------------------------
+template <int W, int HEAD, int MODE>
+struct TcTile {
+  typedef TcGeo<W> G;
+  typedef HeadTraits<HEAD> HT;
+  static constexpr int JK = HT::JK, OUT = HT::OUT;
+  typedef JetTraits<JK> JT;
+  static constexpr int C = JT::C;
+  static constexpr bool VAL = (JK == JET_V);
+  static constexpr int CP = VAL ? 1 : 4;           // rows per point
+  static constexpr int PTS = TR / CP;              // points per tile
+
+  // byte offset of (row r, neuron n) in the hi slabs of the X buffer
+  static TC_DEV uint32_t xoff(int r, int n) {
+    return (uint32_t)(n >> 6) * G::SLAB + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u +
+           ((((uint32_t)(n & 63) >> 3) ^ (uint32_t)(r & 7)) << 4) + (uint32_t)(n & 7) * 2u;
+  }
+  static TC_DEV void store_x(uint8_t* xbuf, int r, int n, float y) {
+    __half h, l;
+    split_f16(y, h, l);
+    const uint32_t o = xoff(r, n);
+    *reinterpret_cast<__half*>(xbuf + o) = h;
+    *reinterpret_cast<__half*>(xbuf + G::KSL * G::SLAB + o) = l;
+  }
+
+  // upper bounds of |a_c| over this thread's points from the pre-activation jet z (no sincos needed)
+  static TC_DEV void bound_update(float om, const float* z, float (&bnd)[4]) {
+    if (!VAL) {
+      bnd[1] = fmaxf(bnd[1], om * fabsf(z[1]));
+      bnd[2] = fmaxf(bnd[2], om * fabsf(z[2]));
+      if (JT::Q) {
+        float pp = 0.f;
+        if (JT::D0) pp += z[1] * z[1];
+        if (JT::D1) pp += z[2] * z[2];
+        bnd[3] = fmaxf(bnd[3], om * fabsf(z[3]) + om * om * pp);
+      }
+    }
+  }
+  // all epilogue threads: fold bounds, barrier, read the shifts of this layer's output; record them in shifts[l]
+  // `seq` counts the calls of this thread (selects the cmax half; the other half is cleared for the next call).
+  static TC_DEV void agree_shifts(TcCtx<W>& cx, int l, int& seq, const float (&bnd)[4], int (&sh)[4], int tid, int lane) {
+    uint32_t* cm = cx.cmax + (seq & 1) * 4;
+    if (!VAL) {
+      fold_max(cm + 1, bnd[1], lane);
+      fold_max(cm + 2, bnd[2], lane);
+      if (JT::Q) fold_max(cm + 3, bnd[3], lane);
+    }
+    epi_sync<G::NEPI>();
+    sh[0] = 14;   // |sin| <= 1
+    sh[1] = sh[2] = sh[3] = 0;
+    if (!VAL) {
+      sh[1] = shift_for_max(__uint_as_float(cm[1]));
+      sh[2] = shift_for_max(__uint_as_float(cm[2]));
+      if (JT::Q) sh[3] = shift_for_max(__uint_as_float(cm[3]));
+    }
+    if (tid == 0) {
+      for (int c = 0; c < 4; ++c) cx.shifts[l * 4 + c] = sh[c];
+      uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 4;
+      other[0] = other[1] = other[2] = other[3] = 0u;
+    }
+    ++seq;
+  }
+
+
+  // ---- the epilogue side of one tile (all W epilogue threads) ------------------------------------------
+  static TC_DEV void run(const TcParams& p, TcCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile,
+                         uint32_t tbase, int& seq, uint32_t& dpar, const int* wshift) {
+    const KParams& kp = p.k;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = tid;                          // this thread's neuron
+    const int mt = n >> 7;
+    const float om = kp.omega;
+    const int L = kp.L;
+    const float* th = kp.th + (size_t)task * kp.th_stride;
+    const float* prm = kp.prm + (size_t)task * kp.nprm;
+    const int pt0 = tile * PTS;
+    const float* pts = sg.pts + (size_t)task * sg.task_stride;
+    const uint32_t tlane = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * TR);
+    float* xs = cx.xs;
+
+    // ---- points ----
+    for (int i = tid; i < PTS; i += G::NEPI) {
+      const int gp = pt0 + i;
+      float x0 = 0.f, x1 = 0.f;
+      if (gp < sg.n) { x0 = pts[2 * (size_t)gp]; x1 = pts[2 * (size_t)gp + 1]; }
+      xs[i] = x0; xs[TR + i] = x1;
+    }
+    // ---- layer 0 (in_dim = 2): direct ----
+    int sh[4];
+    {
+      const float w00 = mpde_ldg(th + n), w01 = mpde_ldg(th + W + n), b0 = mpde_ldg(th + 2 * W + n);
+      float bnd[4] = {0.f, 0.f, 0.f, 0.f};
+      { const float z[4] = {0.f, w00, w01, 0.f}; bound_update(om, z, bnd); }
+      agree_shifts(cx, 0, seq, bnd, sh, tid, lane);     // also orders the xs writes before the reads below
+      float ys[4];
+      for (int c = 0; c < 4; ++c) ys[c] = pow2i(sh[c]);
+      MPDE_NOUNROLL
+      for (int pl = 0; pl < PTS; ++pl) {
+        float z[4], a[4], sv[5];
+        z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[TR + pl], b0));
+        z[1] = w00; z[2] = w01; z[3] = 0.f;
+        jet_act_fwd<JK>(om, z, a, sv);
+        if (VAL) {
+          store_x(cx.xbuf, pl, n, a[0] * ys[0]);
+        } else {
+          MPDE_UNROLL
+          for (int c = 0; c < 4; ++c) store_x(cx.xbuf, 4 * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    mbar_arrive(cx.xready);
+
+    // ---- hidden layers 1..L-1: accumulators from TMEM -> activation -> X (in place) ----
+    for (int l = 1; l < L; ++l) {
+      const float bias = mpde_ldg(th + ph_off_layer(W, l) + 2 * W * W + n);
+      float zs[4];
+      { const int sw = wshift[l]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
+      mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+      tc_fence_after();
+      // pass 1: bounds of the output channels
+      float bnd[4] = {0.f, 0.f, 0.f, 0.f};
+      if (!VAL) {
+        MPDE_NOUNROLL
+        for (int ch = 0; ch < TR / 32; ++ch) {
+          uint32_t v[32];
+          tmem_ld32(tlane + ch * 32, v);
+          tmem_ld_wait();
+          MPDE_UNROLL
+          for (int q = 0; q < 8; ++q) {
+            float z[4];
+            MPDE_UNROLL
+            for (int c = 0; c < 4; ++c) z[c] = __uint_as_float(v[4 * q + c]) * zs[c];
+            bound_update(om, z, bnd);
+          }
+        }
+      }
+      agree_shifts(cx, l, seq, bnd, sh, tid, lane);     // barrier: every MMA of this layer has completed
+      float ys[4];
+      for (int c = 0; c < 4; ++c) ys[c] = pow2i(sh[c]);
+      // pass 2
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < TR / 32; ++ch) {
+        uint32_t v[32];
+        tmem_ld32(tlane + ch * 32, v);
+        tmem_ld_wait();
+        if (VAL) {
+          MPDE_UNROLL
+          for (int q = 0; q < 32; ++q) {
+            float z[1], a[1], sv[2];
+            z[0] = fmaf(__uint_as_float(v[q]), zs[0], bias);
+            jet_act_fwd<JK>(om, z, a, sv);
+            store_x(cx.xbuf, ch * 32 + q, n, a[0] * ys[0]);
+          }
+        } else {
+          MPDE_UNROLL
+          for (int q = 0; q < 8; ++q) {
+            float z[4], a[4], sv[5];
+            MPDE_UNROLL
+            for (int c = 0; c < 4; ++c) z[c] = __uint_as_float(v[4 * q + c]) * zs[c];
+            z[0] += bias;
+            jet_act_fwd<JK>(om, z, a, sv);
+            MPDE_UNROLL
+            for (int c = 0; c < 4; ++c) store_x(cx.xbuf, ch * 32 + 4 * q + c, n, c < C ? a[c] * ys[c] : 0.f);
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(cx.xready);
+    }
+
+    // ---- output layer: D0 lanes 0..OUT-1 hold y[o][row] ----
+    if (mt == 0) {
+      mbar_wait(&cx.dfull[0], dpar); dpar ^= 1u;
+      tc_fence_after();
+      if (warp == 0) {
+        float zs[4];
+        { const int sw = wshift[L]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
+        MPDE_NOUNROLL
+        for (int ch = 0; ch < TR / 32; ++ch) {
+          uint32_t v[32];
+          tmem_ld32(tlane + ch * 32, v);
+          tmem_ld_wait();
+          if (lane < OUT) {
+            MPDE_UNROLL
+            for (int q = 0; q < 32; ++q) cx.ybuf[(ch * 32 + q) * 2 + lane] = __uint_as_float(v[q]) * zs[VAL ? 0 : (q & 3)];
+          }
+        }
+      }
+      tc_fence_before();
+    }
+    epi_sync<G::NEPI>();
+
+    // ---- head: one thread per point ----
+    if (tid < PTS) {
+      const int pl = tid;
+      const float* bL = th + ph_off_out(W, L) + W * OUT;
+      float u[OUT * C], ub[OUT * C];
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o)
+        MPDE_UNROLL
+        for (int c = 0; c < C; ++c) {
+          float y = cx.ybuf[(CP * pl + c) * 2 + o];
+          if (c == 0) y += mpde_ldg(bL + o);
+          u[o * C + c] = y;
+        }
+      const int gp = pt0 + pl;
+      const bool valid = gp < sg.n;
+      float res = 0.f;
+      float val = head_eval<HEAD>(u, xs[pl], xs[TR + pl], prm, sg.coef, ub, &res);
+      if (!valid) val = 0.f;
+      cx.red[pl] = val;
+      if (MODE == MODE_LOSS && valid && sg.res_out != nullptr) {
+        float* ro = sg.res_out + (size_t)task * sg.res_stride;
+        if (HEAD == HEAD_EVAL || HEAD == HEAD_EVAL2) {
+          MPDE_UNROLL
+          for (int o = 0; o < OUT; ++o) ro[(size_t)gp * OUT + o] = u[o * C];
+        } else {
+          ro[gp] = res;
+        }
+      }
+    }
+    epi_sync<G::NEPI>();
+    if (warp == 0) {
+      float s = 0.f;
+      MPDE_UNROLL
+      for (int j = 0; j < PTS / 32; ++j) s += cx.red[lane + 32 * j];
+      MPDE_UNROLL
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) cx.terms[seg_id] += s;
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// kernel: grid = (ctas_per_task, T); each CTA walks the task's tiles with stride gridDim.x
+// ---------------------------------------------------------------------------------------------------------
+template <int W, int PDE, int MODE>
+__global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_constant__ TcParams p) {
+  typedef TcGeo<W> G;
+  TcCtx<W> cx;
+  cx.carve();
+  const KParams& kp = p.k;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int task = blockIdx.y;
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  const int L = kp.L;
+  const int n_tiles = kp.seg_tile_begin[kp.n_seg];
+
+  if (tid == 0) {
+    if (smem_u32(tc_smem_raw) & 1023u) { printf("tc_pde_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
+    for (int i = 0; i < NSTAGE; ++i) { mbar_init(&cx.full[i], 1); mbar_init(&cx.empty[i], 1); }
+    mbar_init(cx.xready, G::NEPI);
+    mbar_init(&cx.dfull[0], 1); mbar_init(&cx.dfull[1], 1);
+    mbar_fence_init();
+    for (int i = 0; i < 8; ++i) cx.cmax[i] = 0u;
+    for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
+  }
+  if (warp == 0) tmem_alloc(cx.tmem_slot, G::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = *cx.tmem_slot;
+
+  if (warp < G::NEPI / 32) {
+    // ===== epilogue warps =====
+    int seq = 0; uint32_t dpar = 0;
+    const int* wshift = p.wshift + (size_t)task * p.wshift_stride;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      int s = 0;
+      while (s + 1 < kp.n_seg && t >= kp.seg_tile_begin[s + 1]) ++s;
+      const int tile = t - kp.seg_tile_begin[s];
+      const SegDesc& sg = kp.seg[s];
+      if (PDE == PDE_POISSON) {
+        if (sg.head == HEAD_POISSON_DOMAIN) TcTile<W, HEAD_POISSON_DOMAIN, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+        else TcTile<W, HEAD_POISSON_BOUNDARY, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+      } else if (PDE == PDE_BURGERS) {
+        if (sg.head == HEAD_BURGERS_DOMAIN) TcTile<W, HEAD_BURGERS_DOMAIN, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+        else TcTile<W, HEAD_BURGERS_IC, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+      } else if (PDE == PDE_HYPER) {
+        if (sg.head == HEAD_HYPER_DOMAIN) TcTile<W, HEAD_HYPER_DOMAIN, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+        else if (sg.head == HEAD_HYPER_TOP) TcTile<W, HEAD_HYPER_TOP, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+        else TcTile<W, HEAD_HYPER_BOTTOM, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+      } else if (PDE == PDE_EVAL1) {
+        TcTile<W, HEAD_EVAL, MODE_LOSS>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+      } else {
+        TcTile<W, HEAD_EVAL2, MODE_LOSS>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
+      }
+    }
+  } else if (warp == G::NEPI / 32) {
+    // ===== producer: stream the weight image through the ring (same stream for every tile) =====
+    if (lane == 0) {
+      const uint8_t* img = p.wimg + (size_t)task * p.wimg_stride;
+      const int nst = (L - 1) * G::NMT * G::KSL + G::KSL;
+      uint32_t stage = 0, phase = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int i = 0; i < nst; ++i) {
+          mbar_wait(&cx.empty[stage], phase ^ 1u);
+          mbar_arrive_expect_tx(&cx.full[stage], STAGE_BYTES);
+          bulk_g2s(cx.ring + (size_t)stage * STAGE_BYTES, img + (size_t)i * STAGE_BYTES, STAGE_BYTES, &cx.full[stage]);
+          if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(FMT_F16, 128, TR, 0, 0);
+      const uint32_t xb = smem_u32(cx.xbuf);
+      uint32_t stage = 0, phase = 0, xpar = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int step = 1; step <= L; ++step) {
+          mbar_wait(cx.xready, xpar); xpar ^= 1u;
+          tc_fence_after();
+          const int nmt = (step < L) ? G::NMT : 1;
+          for (int mt = 0; mt < nmt; ++mt) {
+            const uint32_t d = tbase + (uint32_t)mt * TR;
+            uint32_t acc = 0;
+            for (int s = 0; s < G::KSL; ++s) {
+              mbar_wait(&cx.full[stage], phase);
+              tc_fence_after();
+              const uint32_t a_hi = smem_u32(cx.ring + (size_t)stage * STAGE_BYTES), a_lo = a_hi + 16384u;
+              const uint32_t b_hi = xb + (uint32_t)s * G::SLAB, b_lo = b_hi + (uint32_t)G::KSL * G::SLAB;
+              MPDE_UNROLL
+              for (int kk = 0; kk < 4; ++kk) {
+                const uint64_t ah = desc_kmajor(a_hi + kk * 32), al = desc_kmajor(a_lo + kk * 32);
+                const uint64_t bh = desc_kmajor(b_hi + kk * 32), bl = desc_kmajor(b_lo + kk * 32);
+                mma_f16_ss(d, ah, bh, idesc, acc); acc = 1;
+                mma_f16_ss(d, al, bh, idesc, 1);
+                mma_f16_ss(d, ah, bl, idesc, 1);
+              }
+              tc_commit(&cx.empty[stage]);
+              if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
+            }
+            tc_commit(&cx.dfull[mt]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 0) tmem_dealloc(tbase, G::TMEM_COLS);
+  if (tid < MAX_SEG) kp.partial_terms[(size_t)cta * MAX_SEG + tid] = cx.terms[tid];
+}
+
+}  // namespace tc
+}  // namespace mpde
