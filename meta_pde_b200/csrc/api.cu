@@ -122,7 +122,9 @@ struct EvalPlan {
   // workspace sizes (floats)
   size_t n_th, n_thd, n_scratch, n_pg, n_ph, n_pt, n_gtmp;
   bool tc;                  // tensor-core path
-  size_t n_wimg, n_wshift;  // floats: tc weight image [T][image], shifts [T][16]
+  size_t n_wimg, n_wshift;  // floats: tc weight image [T][image], shifts [T][2*TC_MAX_L]
+  size_t n_rec, n_zsp, n_psmall;          // tc GRAD spills (floats) and per-CTA small-parameter partials
+  long long rec_seg_base[MAX_SEG]; long long rec_per_task, zsp_per_task; int PS;
   size_t bytes;
 };
 
@@ -202,11 +204,29 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   pl->n_gtmp = need_gtmp ? (size_t)T * pl->P : 0;
   pl->n_wimg = 0; pl->n_wshift = 0;
 #ifndef MPDE_EMU
-  if (pl->tc) { pl->n_wimg = (size_t)T * (tc_image_bytes(pl->W, pl->L) / 4); pl->n_wshift = (size_t)T * tc::TC_MAX_L * 2; }
+  pl->n_rec = pl->n_zsp = pl->n_psmall = 0; pl->PS = 0; pl->rec_per_task = pl->zsp_per_task = 0;
+  if (pl->tc) {
+    pl->n_wimg = (size_t)T * (tc_image_bytes(pl->W, pl->L, mode != MODE_LOSS) / 4);
+    pl->n_wshift = (size_t)T * tc::TC_MAX_L * 2;
+    if (mode != MODE_LOSS) {
+      pl->n_scratch = 0; pl->n_pg = 0; pl->n_ph = 0;     // FP32-FMA kernel buffers are not used
+      long long off = 0;
+      for (int s = 0; s < pl->n_seg; ++s) {
+        pl->rec_seg_base[s] = off;
+        const int jk = (pl->head[s] == HEAD_POISSON_DOMAIN) ? JET_LAP : (pl->head[s] == HEAD_BURGERS_DOMAIN) ? JET_XX
+                     : (pl->head[s] == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
+        off += (long long)(pl->tile_begin[s + 1] - pl->tile_begin[s]) * pl->L * tc::rec_fields_points(jk) * pl->W;
+      }
+      pl->rec_per_task = off;
+      pl->zsp_per_task = (long long)tiles * (pl->L - 1) * 128 * pl->W;
+      pl->PS = tc::ps_count(pl->W, pl->L, pl->OUT);
+      pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS;
+    }
+  }
 #endif
   Carver c(nullptr, 0);
   c.take(pl->n_th); c.take(pl->n_thd); c.take(pl->n_scratch); c.take(pl->n_pg); c.take(pl->n_ph); c.take(pl->n_pt); c.take(pl->n_gtmp);
-  c.take(pl->n_wimg); c.take(pl->n_wshift);
+  c.take(pl->n_wimg); c.take(pl->n_wshift); c.take(pl->n_rec); c.take(pl->n_zsp); c.take(pl->n_psmall);
   pl->bytes = c.off + 256;
   return MPDE_OK;
 }
@@ -246,7 +266,8 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   float* th = c.take(pl.n_th); float* thd = c.take(pl.n_thd); float* scratch = c.take(pl.n_scratch);
   float* pg = c.take(pl.n_pg); float* ph = c.take(pl.n_ph); float* pt = c.take(pl.n_pt); float* gtmp = c.take(pl.n_gtmp);
   float* wimg = c.take(pl.n_wimg); float* wshift = c.take(pl.n_wshift);
-  (void)wimg; (void)wshift;
+  float* rec = c.take(pl.n_rec); float* zsp = c.take(pl.n_zsp); float* psmall = c.take(pl.n_psmall);
+  (void)wimg; (void)wshift; (void)rec; (void)zsp; (void)psmall;
   if (mode != MODE_HVP) thd = nullptr;
 
   // 1. prep: theta -> theta-hat (shared theta: prepared once)
@@ -284,8 +305,8 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
 #ifndef MPDE_EMU
   if (pl.tc) {
     // weight image for the tensor-core kernels (hidden kernels from natural theta, output layer from theta-hat)
-    rc = tc_launch_prep(pl.W, pl.L, pl.OUT, T_prep, theta, theta_stride, th, kp.th_stride, (uint8_t*)wimg,
-                        (long long)tc_image_bytes(pl.W, pl.L), (int*)wshift, 2 * tc::TC_MAX_L, stream);
+    rc = tc_launch_prep(pl.W, pl.L, pl.OUT, T_prep, mode != MODE_LOSS, theta, theta_stride, th, kp.th_stride, (uint8_t*)wimg,
+                        (long long)tc_image_bytes(pl.W, pl.L, mode != MODE_LOSS), (int*)wshift, 2 * tc::TC_MAX_L, stream);
     if (rc) return rc;
   }
   cudaEvent_t prof_stop;
@@ -293,11 +314,15 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
 #endif
 #ifndef MPDE_EMU
   if (pl.tc) {
-    const long long img_bytes = (long long)tc_image_bytes(pl.W, pl.L);
+    const long long img_bytes = (long long)tc_image_bytes(pl.W, pl.L, mode != MODE_LOSS);
     tc::TcParams tp;
     tp.k = kp;
     tp.wimg = (const uint8_t*)wimg; tp.wimg_stride = (T_prep == 1) ? 0 : img_bytes;
     tp.wshift = (const int*)wshift; tp.wshift_stride = (T_prep == 1) ? 0 : 2 * tc::TC_MAX_L;
+    tp.rec = rec; tp.rec_task_stride = pl.rec_per_task;
+    for (int s = 0; s < MAX_SEG; ++s) tp.rec_seg_base[s] = (s < pl.n_seg) ? pl.rec_seg_base[s] : 0;
+    tp.zsp = zsp; tp.zsp_task_stride = pl.zsp_per_task;
+    tp.psmall = psmall; tp.PS = pl.PS;
     rc = dispatch_tc(pl.W, pl.pde, mode, 1, &tp, pl.G, T, stream, nullptr);
   } else
 #endif
@@ -323,6 +348,25 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   if (mode == MODE_LOSS) return MPDE_OK;
   // 4. reduce the per-CTA partials, then the chain rule back to theta
   float* gout = grad ? grad : gtmp;
+#ifndef MPDE_EMU
+  if (pl.tc) {
+    // hidden kernels: contraction over the task's rows from the spills; small parameters: fixed-order sum over CTAs
+    tc::TcWgradParams wp;
+    wp.W = pl.W; wp.L = pl.L; wp.T = T; wp.n_seg = pl.n_seg; wp.omega = net->omega;
+    for (int s = 0; s <= pl.n_seg; ++s) wp.seg_tile_begin[s] = pl.tile_begin[s];
+    for (int s = 0; s < pl.n_seg; ++s) {
+      wp.seg_jk[s] = (pl.head[s] == HEAD_POISSON_DOMAIN) ? JET_LAP : (pl.head[s] == HEAD_BURGERS_DOMAIN) ? JET_XX
+                   : (pl.head[s] == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
+      wp.rec_seg_base[s] = pl.rec_seg_base[s];
+    }
+    wp.rec = rec; wp.rec_task_stride = pl.rec_per_task; wp.zsp = zsp; wp.zsp_task_stride = pl.zsp_per_task;
+    wp.gout = gout; wp.g_stride = pl.P;
+    rc = tc_launch_wgrad(&wp, stream);
+    if (rc) return rc;
+    rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall, gout, pl.P, stream);
+    if (rc) return rc;
+  } else
+#endif
   {
     ReduceParams rp;
     rp.P = pl.P; rp.G = pl.G;

@@ -24,11 +24,14 @@ int dispatch_w256(int pde, int mode, int op, const KParams* p, int gx, int gy, v
 
 // tensor-core (tcgen05) path, widths 128 / 256 (tc_inst.cu; not part of the emulator build)
 #ifndef MPDE_EMU
-namespace tc { struct TcParams; }
+namespace tc { struct TcParams; struct TcWgradParams; }
 bool tc_supported(int W, int L, int mode);
 int dispatch_tc(int W, int pde, int mode, int op, const tc::TcParams* p, int gx, int gy, void* stream, KernelInfo* info);
-size_t tc_image_bytes(int W, int L);
-int tc_launch_prep(int W, int L, int OUT, int T, const float* theta, long long theta_stride, const float* th,
+size_t tc_image_bytes(int W, int L, int with_bwd);
+int tc_launch_wgrad(const tc::TcWgradParams* p, void* stream);
+int tc_launch_reduce_small(int W, int L, int OUT, int PS, int G, int T, const float* ps, float* gout, long long g_stride,
+                           void* stream);
+int tc_launch_prep(int W, int L, int OUT, int T, int with_bwd, const float* theta, long long theta_stride, const float* th,
                    long long th_stride, uint8_t* wimg, long long wimg_stride, int* wshift, long long wshift_stride,
                    void* stream);
 #endif

@@ -1,6 +1,7 @@
 // tc_inst.cu -- instantiation and launch of the tensor-core (tcgen05) jet kernels for widths 128 and 256.
 #include "host_common.h"
 #include "tc_kernels.cuh"
+#include "tc_wgrad.cuh"
 #include <mutex>
 
 namespace mpde {
@@ -26,6 +27,14 @@ static int tc_run_inst(int op, const TcParams* p, int gx, int gy, void* stream, 
 
 template <int W>
 static int tc_run_width(int pde, int mode, int op, const TcParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  if (mode == MODE_GRAD) {
+    switch (pde) {
+      case PDE_POISSON: return tc_run_inst<W, PDE_POISSON, MODE_GRAD>(op, p, gx, gy, stream, info);
+      case PDE_BURGERS: return tc_run_inst<W, PDE_BURGERS, MODE_GRAD>(op, p, gx, gy, stream, info);
+      case PDE_HYPER:   return tc_run_inst<W, PDE_HYPER, MODE_GRAD>(op, p, gx, gy, stream, info);
+    }
+    return 1;
+  }
   if (mode != MODE_LOSS) return 1;
   switch (pde) {
     case PDE_POISSON: return tc_run_inst<W, PDE_POISSON, MODE_LOSS>(op, p, gx, gy, stream, info);
@@ -39,7 +48,7 @@ static int tc_run_width(int pde, int mode, int op, const TcParams* p, int gx, in
 
 // modes the tensor-core path implements for this width / depth (the FP32-FMA kernels serve everything else)
 bool tc_supported(int W, int L, int mode) {
-  return (W == 128 || W == 256) && L >= 2 && L <= TC_MAX_L && mode == MODE_LOSS;
+  return (W == 128 || W == 256) && L >= 2 && L <= TC_MAX_L && (mode == MODE_LOSS || mode == MODE_GRAD);
 }
 
 int dispatch_tc(int W, int pde, int mode, int op, const TcParams* p, int gx, int gy, void* stream, KernelInfo* info) {
@@ -48,18 +57,62 @@ int dispatch_tc(int W, int pde, int mode, int op, const TcParams* p, int gx, int
   return 1;
 }
 
-size_t tc_image_bytes(int W, int L) { return W == 128 ? TcGeo<128>::image_bytes(L) : TcGeo<256>::image_bytes(L); }
+size_t tc_image_bytes(int W, int L, int with_bwd) {
+  return W == 128 ? TcGeo<128>::image_bytes(L, with_bwd != 0) : TcGeo<256>::image_bytes(L, with_bwd != 0);
+}
 
-int tc_launch_prep(int W, int L, int OUT, int T, const float* theta, long long theta_stride, const float* th,
+int tc_launch_prep(int W, int L, int OUT, int T, int with_bwd, const float* theta, long long theta_stride, const float* th,
                    long long th_stride, uint8_t* wimg, long long wimg_stride, int* wshift, long long wshift_stride,
                    void* stream) {
   TcPrepParams pp;
-  pp.W = W; pp.L = L; pp.OUT = OUT; pp.T = T;
+  pp.W = W; pp.L = L; pp.OUT = OUT; pp.T = T; pp.with_bwd = with_bwd;
   pp.theta = theta; pp.theta_stride = theta_stride; pp.th = th; pp.th_stride = th_stride;
   pp.wimg = wimg; pp.wimg_stride = wimg_stride; pp.wshift = wshift; pp.wshift_stride = wshift_stride;
-  const int stages = (int)(tc_image_bytes(W, L) / STAGE_BYTES);
+  const int stages = (int)(tc_image_bytes(W, L, with_bwd) / STAGE_BYTES);
   g_launches++;
   tc_prep_kernel<<<dim3(stages, T, 1), dim3(256, 1, 1), 0, (cudaStream_t)stream>>>(pp);
+  return cudaGetLastError() != cudaSuccess ? 4 : 0;
+}
+
+
+// ---- hidden-layer weight gradients from the spills (tc_wgrad.cuh) ----
+int tc_launch_wgrad(const TcWgradParams* p, void* stream) {
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&]() {
+    attr_err = cudaFuncSetAttribute(tc_wgrad_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgGeo<128>::SMEM);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(tc_wgrad_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgGeo<256>::SMEM);
+  });
+  if (attr_err != cudaSuccess) return 4;
+  g_launches++;
+  const dim3 grid((p->W / 128) * (p->L - 1), p->T, 1);
+  if (p->W == 128) tc_wgrad_kernel<128><<<grid, dim3(WgGeo<128>::NT, 1, 1), WgGeo<128>::SMEM, (cudaStream_t)stream>>>(*p);
+  else tc_wgrad_kernel<256><<<grid, dim3(WgGeo<256>::NT, 1, 1), WgGeo<256>::SMEM, (cudaStream_t)stream>>>(*p);
+  return cudaGetLastError() != cudaSuccess ? 4 : 0;
+}
+
+// ---- fixed-order sum of the per-CTA small-parameter partials into the natural gradient layout ----
+struct ReduceSmallParams { int W, L, OUT, PS, G; const float* ps; float* gout; long long g_stride; };
+__global__ void __launch_bounds__(256) tc_reduce_small_kernel(ReduceSmallParams p) {
+  const int t = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.PS) return;
+  const float* src = p.ps + (size_t)t * p.G * p.PS + i;
+  float s = 0.f;
+  for (int c = 0; c < p.G; ++c) s += src[(size_t)c * p.PS];
+  const int W = p.W, L = p.L, OUT = p.OUT;
+  int dst;
+  if (i < 3 * W) dst = i;                                                     // w0 [2][W], b0 [W]
+  else if (i < (L + 2) * W) { const int l = (i - 2 * W) / W, n = i % W; dst = nat_off_layer(W, l) + W * W + n; }   // b_l
+  else dst = nat_off_out(W, L) + (i - (L + 2) * W);                           // wL [W][OUT], bL [OUT]
+  p.gout[(size_t)t * p.g_stride + dst] = s;
+}
+int tc_launch_reduce_small(int W, int L, int OUT, int PS, int G, int T, const float* ps, float* gout, long long g_stride,
+                           void* stream) {
+  ReduceSmallParams rp{W, L, OUT, PS, G, ps, gout, g_stride};
+  g_launches++;
+  tc_reduce_small_kernel<<<dim3((PS + 255) / 256, T, 1), dim3(256, 1, 1), 0, (cudaStream_t)stream>>>(rp);
   return cudaGetLastError() != cudaSuccess ? 4 : 0;
 }
 

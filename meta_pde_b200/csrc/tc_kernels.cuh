@@ -45,7 +45,7 @@ template <int W> struct TcGeo {
   // global weight image per task: hidden layers 1..L-1 (forward copy: NMT*KSL stages each), then the output layer
   static constexpr size_t layer_bytes() { return (size_t)NMT * KSL * STAGE_BYTES; }
   static constexpr size_t out_bytes() { return (size_t)KSL * STAGE_BYTES; }
-  static size_t image_bytes(int L) { return (size_t)(L - 1) * layer_bytes() + out_bytes(); }
+  static size_t image_bytes(int L, bool with_bwd) { return (size_t)(L - 1) * layer_bytes() * (with_bwd ? 2 : 1) + out_bytes(); }
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -54,6 +54,7 @@ template <int W> struct TcGeo {
 // ---------------------------------------------------------------------------------------------------------
 struct TcPrepParams {
   int W, L, OUT, T;
+  int with_bwd;                                 // also write the adjoint copies (layers L-1..1, A operand = W_l [k][n])
   const float* theta; long long theta_stride;   // natural parameters (or the HVP direction)
   const float* th;    long long th_stride;      // theta-hat (effective output layer wLe [W][OUT])
   uint8_t* wimg; long long wimg_stride;
@@ -76,9 +77,12 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(TcPrepParams p) {
   const int t = blockIdx.y;
   const int st = blockIdx.x;                          // stage index inside the task image
   const int per_layer = NMT * KSL;
-  const bool is_out = st >= (L - 1) * per_layer;
-  const int l = is_out ? L : 1 + st / per_layer;      // step index (hidden layer l, or L = output layer)
-  const int rem = is_out ? st - (L - 1) * per_layer : st % per_layer;
+  const int nst_fwd = (L - 1) * per_layer + KSL;
+  const bool is_bwd = st >= nst_fwd;
+  const bool is_out = !is_bwd && st >= (L - 1) * per_layer;
+  // step index: hidden layer l, or L = output layer; adjoint copies run l = L-1 .. 1
+  const int l = is_bwd ? (L - 1) - (st - nst_fwd) / per_layer : (is_out ? L : 1 + st / per_layer);
+  const int rem = is_bwd ? (st - nst_fwd) % per_layer : (is_out ? st - (L - 1) * per_layer : st % per_layer);
   const int mt = is_out ? 0 : rem / KSL, s = is_out ? rem : rem % KSL;
   const float* src = is_out ? p.th + (size_t)t * p.th_stride + ph_off_out(W, L)
                             : p.theta + (size_t)t * p.theta_stride + nat_off_layer(W, l);
@@ -94,13 +98,14 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(TcPrepParams p) {
   }
   const int sh = shift_for_max(red[0]);
   const float sc = pow2i(sh);
-  if (rem == 0 && threadIdx.x == 0) p.wshift[(size_t)t * p.wshift_stride + l] = sh;
+  if (rem == 0 && !is_bwd && threadIdx.x == 0) p.wshift[(size_t)t * p.wshift_stride + l] = sh;
   uint8_t* dst = p.wimg + (size_t)t * p.wimg_stride + (size_t)st * STAGE_BYTES;
   for (int i = threadIdx.x; i < 128 * 64; i += 256) {
     const int m = i >> 6, kk = i & 63;
     const int n = mt * 128 + m, k = s * 64 + kk;
     float w;
     if (is_out) w = (m < OUT) ? src[k * OUT + m] : 0.f;
+    else if (is_bwd) w = src[(size_t)n * W + k];     // adjoint copy: row m = input neuron, K runs over output neurons
     else w = src[(size_t)k * W + n];
     __half h, lo;
     split_f16(w * sc, h, lo);
@@ -188,15 +193,17 @@ struct TcTile {
   }
   // all epilogue threads: fold bounds, barrier, read the shifts of this layer's output; record them in shifts[l]
   // `seq` counts the calls of this thread (selects the cmax half; the other half is cleared for the next call).
+  template <bool ALL = false>
   static TC_DEV void agree_shifts(TcCtx<W>& cx, int l, int& seq, const float (&bnd)[4], int (&sh)[4], int tid, int lane) {
     uint32_t* cm = cx.cmax + (seq & 1) * 4;
+    if (ALL) fold_max(cm + 0, bnd[0], lane);
     if (!VAL) {
       fold_max(cm + 1, bnd[1], lane);
       fold_max(cm + 2, bnd[2], lane);
       if (JT::Q) fold_max(cm + 3, bnd[3], lane);
     }
     epi_sync<G::NEPI>();
-    sh[0] = 14;   // |sin| <= 1
+    sh[0] = ALL ? shift_for_max(__uint_as_float(cm[0])) : 14;   // forward value channel: |sin| <= 1
     sh[1] = sh[2] = sh[3] = 0;
     if (!VAL) {
       sh[1] = shift_for_max(__uint_as_float(cm[1]));
@@ -204,7 +211,7 @@ struct TcTile {
       if (JT::Q) sh[3] = shift_for_max(__uint_as_float(cm[3]));
     }
     if (tid == 0) {
-      for (int c = 0; c < 4; ++c) cx.shifts[l * 4 + c] = sh[c];
+      if (!ALL) { for (int c = 0; c < 4; ++c) cx.shifts[l * 4 + c] = sh[c]; }
       uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 4;
       other[0] = other[1] = other[2] = other[3] = 0u;
     }
@@ -227,6 +234,11 @@ struct TcTile {
     const float* pts = sg.pts + (size_t)task * sg.task_stride;
     const uint32_t tlane = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * TR);
     float* xs = cx.xs;
+    constexpr int NF = JT::NF;
+    // activation records of this tile: [layer][field][point][neuron]
+    float* recp = nullptr;
+    if (MODE != MODE_LOSS)
+      recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NF * PTS) * W + n;
 
     // ---- points ----
     for (int i = tid; i < PTS; i += G::NEPI) {
@@ -250,6 +262,10 @@ struct TcTile {
         z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[TR + pl], b0));
         z[1] = w00; z[2] = w01; z[3] = 0.f;
         jet_act_fwd<JK>(om, z, a, sv);
+        if (MODE != MODE_LOSS) {
+          MPDE_UNROLL
+          for (int f = 0; f < NF; ++f) recp[(size_t)(f * PTS + pl) * W] = sv[f];
+        }
         if (VAL) {
           store_x(cx.xbuf, pl, n, a[0] * ys[0]);
         } else {
@@ -301,6 +317,10 @@ struct TcTile {
             float z[1], a[1], sv[2];
             z[0] = fmaf(__uint_as_float(v[q]), zs[0], bias);
             jet_act_fwd<JK>(om, z, a, sv);
+            if (MODE != MODE_LOSS) {
+              MPDE_UNROLL
+              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f) * PTS + ch * 32 + q) * W] = sv[f];
+            }
             store_x(cx.xbuf, ch * 32 + q, n, a[0] * ys[0]);
           }
         } else {
@@ -311,6 +331,10 @@ struct TcTile {
             for (int c = 0; c < 4; ++c) z[c] = __uint_as_float(v[4 * q + c]) * zs[c];
             z[0] += bias;
             jet_act_fwd<JK>(om, z, a, sv);
+            if (MODE != MODE_LOSS) {
+              MPDE_UNROLL
+              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f) * PTS + ch * 8 + q) * W] = sv[f];
+            }
             MPDE_UNROLL
             for (int c = 0; c < 4; ++c) store_x(cx.xbuf, ch * 32 + 4 * q + c, n, c < C ? a[c] * ys[c] : 0.f);
           }
@@ -362,6 +386,13 @@ struct TcTile {
       float val = head_eval<HEAD>(u, xs[pl], xs[TR + pl], prm, sg.coef, ub, &res);
       if (!valid) val = 0.f;
       cx.red[pl] = val;
+      if (MODE != MODE_LOSS) {
+        // ybuf now carries the seeds ybar[row][o] of the reverse pass (zero for padding points / channels)
+        MPDE_UNROLL
+        for (int o = 0; o < OUT; ++o)
+          MPDE_UNROLL
+          for (int c = 0; c < CP; ++c) cx.ybuf[(CP * pl + c) * 2 + o] = (valid && c < C) ? ub[o * C + c] : 0.f;
+      }
       if (MODE == MODE_LOSS && valid && sg.res_out != nullptr) {
         float* ro = sg.res_out + (size_t)task * sg.res_stride;
         if (HEAD == HEAD_EVAL || HEAD == HEAD_EVAL2) {
@@ -380,6 +411,106 @@ struct TcTile {
       MPDE_UNROLL
       for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
       if (lane == 0) cx.terms[seg_id] += s;
+    }
+    if (MODE == MODE_LOSS) return;
+
+    // =====================================================================================================
+    // reverse pass: thread n owns neuron n of every layer.  abar_l comes from the seeds (l = L-1) or
+    // from the adjoint contraction D[k][row] = sum_n W_{l+1}[k][n] zbar_{l+1}[row][n] in TMEM; zbar_l goes (a) in fp32
+    // to the spill read by tc_wgrad_kernel and (b) as fp16 hi/lo into X, the B operand of the next adjoint contraction.
+    // =====================================================================================================
+    float* ps = p.psmall + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
+    float* zsp_tile = p.zsp + (size_t)task * p.zsp_task_stride +
+                      (size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) * TR * W + n;
+    float wl[OUT];
+    MPDE_UNROLL
+    for (int o = 0; o < OUT; ++o) wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
+    if (tid < OUT) {   // output bias: sum of the value-channel seeds
+      float g = 0.f;
+      for (int pl = 0; pl < PTS; ++pl) g += cx.ybuf[(CP * pl) * 2 + tid];
+      ps[ps_off_wl(W, L) + W * OUT + tid] += g;
+    }
+    int shz[4] = {0, 0, 0, 0};
+    for (int l = L - 1; l >= 0; --l) {
+      float zs[4] = {0.f, 0.f, 0.f, 0.f};
+      if (l < L - 1) {
+        const int sw = wshift[l + 1];
+        for (int c = 0; c < 4; ++c) zs[c] = pow2i(-shz[c] - sw);
+        mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+        tc_fence_after();
+      }
+      float bnd[4] = {0.f, 0.f, 0.f, 0.f};
+      float bsum = 0.f, g0 = 0.f, g1 = 0.f, gw[OUT];
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o) gw[o] = 0.f;
+      float* zl = zsp_tile + (size_t)(l - 1) * TR * W;     // only dereferenced for l >= 1
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < TR / 32; ++ch) {
+        uint32_t v[32];
+        if (l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
+        constexpr int PPC = 32 / CP;                      // points per 32-row chunk
+        MPDE_UNROLL
+        for (int q = 0; q < PPC; ++q) {
+          const int pl = ch * PPC + q;
+          float ab[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zb[4] = {0.f, 0.f, 0.f, 0.f};
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) {
+            if (l < L - 1) {
+              ab[c] = __uint_as_float(v[CP * q + c]) * zs[c];
+            } else {
+              float a_ = 0.f;
+              MPDE_UNROLL
+              for (int o = 0; o < OUT; ++o) a_ = fmaf(wl[o], cx.ybuf[(CP * pl + c) * 2 + o], a_);
+              ab[c] = a_;
+            }
+          }
+          MPDE_UNROLL
+          for (int f = 0; f < NF; ++f) sv[f] = recp[(size_t)((l * NF + f) * PTS + pl) * W];
+          jet_act_bwd<JK>(om, sv, ab, zb);
+          bsum += zb[0];
+          if (l == L - 1) {
+            float a[4];
+            jet_act_from_saved<JK>(om, sv, a);
+            MPDE_UNROLL
+            for (int o = 0; o < OUT; ++o)
+              MPDE_UNROLL
+              for (int c = 0; c < C; ++c) gw[o] = fmaf(a[c], cx.ybuf[(CP * pl + c) * 2 + o], gw[o]);
+          }
+          if (l == 0) {
+            if (VAL) { g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[TR + pl], zb[0], g1); }
+            else { g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[TR + pl], zb[0], zb[2]); }
+          } else {
+            MPDE_UNROLL
+            for (int c = 0; c < CP; ++c) {
+              const float z_ = c < C ? zb[c] : 0.f;
+              zl[(size_t)(CP * pl + c) * W] = z_;
+              bnd[c] = fmaxf(bnd[c], fabsf(z_));
+            }
+          }
+        }
+      }
+      // small-parameter gradients: owner-computes read-modify-write into this CTA's partial
+      ps[ps_off_bias(W, l) + n] += bsum;
+      if (l == L - 1) {
+        MPDE_UNROLL
+        for (int o = 0; o < OUT; ++o) ps[ps_off_wl(W, L) + n * OUT + o] += gw[o];
+      }
+      if (l == 0) { ps[n] += g0; ps[W + n] += g1; break; }
+      // zbar_l -> X (B operand of the adjoint contraction with W_l)
+      agree_shifts<true>(cx, l, seq, bnd, shz, tid, lane);      // barrier: all adjoint MMAs that read X have completed
+      float ys[4];
+      for (int c = 0; c < 4; ++c) ys[c] = pow2i(shz[c]);
+      MPDE_NOUNROLL
+      for (int r0 = 0; r0 < TR; r0 += 8) {
+        float zv[8];
+        MPDE_UNROLL
+        for (int j = 0; j < 8; ++j) zv[j] = zl[(size_t)(r0 + j) * W];
+        MPDE_UNROLL
+        for (int j = 0; j < 8; ++j) store_x(cx.xbuf, r0 + j, n, zv[j] * ys[VAL ? 0 : (j & 3)]);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(cx.xready);
     }
   }
 };
@@ -409,10 +540,18 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
     for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
   }
   if (warp == 0) tmem_alloc(cx.tmem_slot, G::TMEM_COLS);
+  if (MODE != MODE_LOSS) {
+    float* ps = p.psmall + (size_t)cta * p.PS;
+    for (int i = tid; i < p.PS; i += G::NT) ps[i] = 0.f;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = *cx.tmem_slot;
+  // weight-image stages per tile: forward hidden layers + output layer (+ the adjoint copies, layers L-1..1)
+  const int nst_fwd = (L - 1) * G::NMT * G::KSL + G::KSL;
+  const int nst_tile = nst_fwd + (MODE != MODE_LOSS ? (L - 1) * G::NMT * G::KSL : 0);
+  const int nsteps = (MODE != MODE_LOSS) ? 2 * L - 1 : L;    // contractions per tile
 
   if (warp < G::NEPI / 32) {
     // ===== epilogue warps =====
@@ -443,10 +582,9 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
     // ===== producer: stream the weight image through the ring (same stream for every tile) =====
     if (lane == 0) {
       const uint8_t* img = p.wimg + (size_t)task * p.wimg_stride;
-      const int nst = (L - 1) * G::NMT * G::KSL + G::KSL;
       uint32_t stage = 0, phase = 0;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        for (int i = 0; i < nst; ++i) {
+        for (int i = 0; i < nst_tile; ++i) {
           mbar_wait(&cx.empty[stage], phase ^ 1u);
           mbar_arrive_expect_tx(&cx.full[stage], STAGE_BYTES);
           bulk_g2s(cx.ring + (size_t)stage * STAGE_BYTES, img + (size_t)i * STAGE_BYTES, STAGE_BYTES, &cx.full[stage]);
@@ -461,10 +599,10 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
       const uint32_t xb = smem_u32(cx.xbuf);
       uint32_t stage = 0, phase = 0, xpar = 0;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        for (int step = 1; step <= L; ++step) {
+        for (int step = 1; step <= nsteps; ++step) {
           mbar_wait(cx.xready, xpar); xpar ^= 1u;
           tc_fence_after();
-          const int nmt = (step < L) ? G::NMT : 1;
+          const int nmt = (step != L) ? G::NMT : 1;   // step L is the output layer (one M tile)
           for (int mt = 0; mt < nmt; ++mt) {
             const uint32_t d = tbase + (uint32_t)mt * TR;
             uint32_t acc = 0;

@@ -11,8 +11,35 @@ struct TcParams {
   KParams k;                       // segments, points, pde params, theta-hat (first layer, biases, output layer)
   const uint8_t* wimg;             // [T or 1][image_bytes]   forward weight image (tc_prep_kernel)
   long long wimg_stride;           // bytes between tasks (0: shared)
-  const int* wshift;               // [T or 1][TC_MAX_L]     weight shift per step (hidden layers 1..L-1, output layer at L)
+  const int* wshift;               // [T or 1][2*TC_MAX_L]   weight shift per step (hidden layers 1..L-1, output layer at L)
   long long wshift_stride;
+  // GRAD / HVP (spills consumed by tc_wgrad_kernel; all indexed per task)
+  float* rec;                      // activation records: per (seg tile, layer): [NF][PTS][W]
+  long long rec_task_stride;       // floats
+  long long rec_seg_base[MAX_SEG]; // floats, first tile of the segment inside the task's block
+  float* zsp;                      // pre-activation adjoints zbar_l, l = 1..L-1: per (task tile, l-1): [TR rows][W]
+  long long zsp_task_stride;       // floats
+  float* psmall;                   // [T][G][PS] per-CTA partials of the small parameters (first/last layer, biases)
+  int PS;
+};
+
+// per-CTA partial layout of the small parameters: w0 [2][W], b0 [W], b_l [W] (l = 1..L-1), wL [W][OUT], bL [OUT]
+MPDE_HD int ps_off_bias(int W, int l) { return 2 * W + l * W; }                  // l = 0..L-1
+MPDE_HD int ps_off_wl(int W, int L) { return (L + 2) * W; }
+MPDE_HD int ps_count(int W, int L, int OUT) { return (L + 2) * W + W * OUT + OUT; }
+// floats of activation records per (tile, layer): NF * PTS * W
+MPDE_HD int rec_fields_points(int jk) { return jk == JET_V ? 2 * 128 : (jk == JET_G ? 4 * 32 : 5 * 32); }
+
+
+struct TcWgradParams {
+  int W, L, T, n_seg;
+  float omega;
+  int seg_tile_begin[MAX_SEG + 1];
+  int seg_jk[MAX_SEG];
+  long long rec_seg_base[MAX_SEG];
+  const float* rec; long long rec_task_stride;
+  const float* zsp; long long zsp_task_stride;
+  float* gout; long long g_stride;          // [T][P] natural layout; hidden kernels are written (not accumulated)
 };
 
 }  // namespace tc

@@ -105,16 +105,18 @@ __global__ void __launch_bounds__(128, 1) gemm_kmajor_kernel(const float* A, con
 // 2. Weight-gradient contraction D[m][n] = sum_r H[r][m] * Z[r][n], M = 128, N = 256, both operands MN-major
 //    (fp16 hi/lo, 3 terms), read from slabs laid out exactly as the K-major activation buffers [row][k].
 // ---------------------------------------------------------------------------------------------------------
-template <int R>
+template <int R, int KIND>
 __global__ void __launch_bounds__(128, 1) gemm_mnmajor_kernel(const float* H, const float* Z, float* D) {
   constexpr int M = 128, N = 256;
-  constexpr uint32_t SLAB = R * 128;   // one slab = 64 fp16 columns of all R rows
+  constexpr int EB = KIND == 0 ? 2 : 4, CPS = 128 / EB;   // columns per slab
+  constexpr int KSTEP = 32 / EB;                          // rows of r per MMA
+  constexpr uint32_t SLAB = R * 128;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* h_hi = smem;
-  uint8_t* h_lo = h_hi + (M / 64) * SLAB;
-  uint8_t* z_hi = h_lo + (M / 64) * SLAB;
-  uint8_t* z_lo = z_hi + (N / 64) * SLAB;
+  uint8_t* h_lo = h_hi + (M / CPS) * SLAB;
+  uint8_t* z_hi = h_lo + (M / CPS) * SLAB;
+  uint8_t* z_lo = z_hi + (N / CPS) * SLAB;
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -127,11 +129,18 @@ __global__ void __launch_bounds__(128, 1) gemm_mnmajor_kernel(const float* H, co
     uint8_t* lo = mat == 0 ? h_lo : z_lo;
     for (int i = tid; i < R * cols; i += 128) {
       const int r = i / cols, c = i % cols;
-      __half h, l;
-      split_f16(src[i], h, l);
-      const uint32_t off = (c / 64) * SLAB + sw128_off(r, (c % 64) * 2);
-      *reinterpret_cast<__half*>(hi + off) = h;
-      *reinterpret_cast<__half*>(lo + off) = l;
+      const uint32_t off = (c / CPS) * SLAB + sw128_off(r, (c % CPS) * EB);
+      if (KIND == 0) {
+        __half h, l;
+        split_f16(src[i], h, l);
+        *reinterpret_cast<__half*>(hi + off) = h;
+        *reinterpret_cast<__half*>(lo + off) = l;
+      } else {
+        const float x = src[i];
+        const float h = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+        *reinterpret_cast<float*>(hi + off) = h;
+        *reinterpret_cast<float*>(lo + off) = x - h;
+      }
     }
   }
   fence_proxy_async_smem();
@@ -140,15 +149,15 @@ __global__ void __launch_bounds__(128, 1) gemm_mnmajor_kernel(const float* H, co
   tc_fence_after();
   const uint32_t tbase = tmem_slot;
   if (tid == 0) {
-    constexpr uint32_t idesc = make_idesc(FMT_F16, M, N, 1, 1);
+    constexpr uint32_t idesc = make_idesc(KIND == 0 ? FMT_F16 : FMT_TF32, M, N, 1, 1);
     uint32_t acc = 0;
     for (int term = 0; term < 3; ++term) {
       const uint8_t* pa = (term == 1) ? h_lo : h_hi;
       const uint8_t* pb = (term == 2) ? z_lo : z_hi;
-      for (int j = 0; j < R / 16; ++j) {   // 16 rows of r per MMA = two 8-row atoms
-        const uint64_t ad = desc_mnmajor(smem_u32(pa) + j * 2048, SLAB);
-        const uint64_t bd = desc_mnmajor(smem_u32(pb) + j * 2048, SLAB);
-        mma_f16_ss(tbase, ad, bd, idesc, acc);
+      for (int j = 0; j < R / KSTEP; ++j) {
+        const uint64_t ad = desc_mnmajor(smem_u32(pa) + j * (KSTEP / 8) * 1024, SLAB);
+        const uint64_t bd = desc_mnmajor(smem_u32(pb) + j * (KSTEP / 8) * 1024, SLAB);
+        if (KIND == 0) mma_f16_ss(tbase, ad, bd, idesc, acc); else mma_tf32_ss(tbase, ad, bd, idesc, acc);
         acc = 1;
       }
     }
@@ -294,7 +303,7 @@ static void run_kmajor(const char* name) {
   cudaFree(dA); cudaFree(dB); cudaFree(dD);
 }
 
-template <int R>
+template <int R, int KIND>
 static void run_mnmajor() {
   unsigned seed = 99u + R;
   std::vector<float> H(R * 128), Z(R * 256), D(128 * 256);
@@ -312,14 +321,14 @@ static void run_mnmajor() {
   CK(cudaMemcpy(dH, H.data(), H.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(dZ, Z.data(), Z.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemset(dD, 0, D.size() * 4));
-  const int smem = 2 * (2 + 4) * R * 128 + 1024;
-  auto kern = gemm_mnmajor_kernel<R>;
+  const int smem = 2 * (128 + 256) * R * (KIND == 0 ? 2 : 4) + 1024;
+  auto kern = gemm_mnmajor_kernel<R, KIND>;
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   kern<<<1, 128, smem>>>(dH, dZ, dD);
   CK(cudaGetLastError());
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost));
-  printf("{\"probe\": \"gemm_mnmajor_wgrad\", \"kind\": \"f16x3\", \"R\": %d, \"rel_l2\": %.3e}\n", R, rel_l2(D, ref));
+  printf("{\"probe\": \"gemm_mnmajor_wgrad\", \"kind\": \"%s\", \"R\": %d, \"rel_l2\": %.3e}\n", KIND == 0 ? "f16x3" : "tf32x3", R, rel_l2(D, ref));
   fflush(stdout);
   cudaFree(dH); cudaFree(dZ); cudaFree(dD);
 }
@@ -390,7 +399,7 @@ int main(int argc, char** argv) {
     run_kmajor<0, 3, 64, 128>("f16");
     run_kmajor<0, 3, 256, 64>("f16");
   }
-  if (what & 2) { run_mnmajor<64>(); run_mnmajor<128>(); }
+  if (what & 2) { run_mnmajor<64, 0>(); run_mnmajor<128, 0>(); run_mnmajor<32, 1>(); run_mnmajor<64, 1>(); }
   if (what & 4) {
     run_rate<0, 256>("f16", sms); run_rate<0, 128>("f16", sms); run_rate<0, 64>("f16", sms);
     run_rate<1, 256>("tf32", sms); run_rate<1, 128>("tf32", sms); run_rate<1, 64>("tf32", sms);
