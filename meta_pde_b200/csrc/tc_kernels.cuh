@@ -495,7 +495,7 @@ struct TcTile {
         MPDE_UNROLL
         for (int o = 0; o < OUT; ++o) ps[ps_off_wl(W, L) + n * OUT + o] += gw[o];
       }
-      if (l == 0) { ps[n] += g0; ps[W + n] += g1; break; }
+      if (l == 0) { ps[n] += g0; ps[W + n] += g1; epi_sync<G::NEPI>(); break; }   // xs is rewritten by the next tile
       // zbar_l -> X (B operand of the adjoint contraction with W_l)
       agree_shifts<true>(cx, l, seq, bnd, shz, tid, lane);      // barrier: all adjoint MMAs that read X have completed
       float ys[4];

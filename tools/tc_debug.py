@@ -8,7 +8,7 @@ from meta_pde_b200 import ops
 from meta_pde_b200._abi import PDE_OUT_DIM
 
 K = ops.kernels(torch.device("cuda:0"))
-for pde, W, L, n, T in [("poisson", 128, 2, 200, 2), ("poisson", 256, 3, 300, 1), ("hyper_elasticity", 128, 3, 100, 1)]:
+for pde, W, L, n, T in [("poisson", 256, 3, 300, 1), ("poisson", 256, 3, 3000, 1), ("poisson", 256, 3, 16384, 1), ("hyper_elasticity", 128, 3, 100, 1)]:
     theta, sets, prm = pc.make_problem(pde, W, L, n, T, 0, True, None)
     OUT = PDE_OUT_DIM[pde]
     net = K.net_desc(L, W, OUT, 30.0, True)
