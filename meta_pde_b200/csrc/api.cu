@@ -124,6 +124,7 @@ struct EvalPlan {
   bool tc;                  // tensor-core path
   size_t n_wimg, n_wshift;  // floats: tc weight image [T][image], shifts [T][2*TC_MAX_L]
   size_t n_rec, n_zsp, n_psmall;          // tc GRAD spills (floats) and per-CTA small-parameter partials
+  size_t n_wimg_d, n_wshift_d, n_zspd, n_psmall_h;   // tc HVP: direction image / shifts, zbardot spill, H v partials
   long long rec_seg_base[MAX_SEG]; long long rec_per_task, zsp_per_task; int PS;
   size_t bytes;
 };
@@ -161,7 +162,8 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   }
   pl->tc = use_tc_path(pl->W, pl->L, mode);
 #ifndef MPDE_EMU
-  if (pl->tc) rc = dispatch_tc(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
+  if (pl->tc && mode == MODE_HVP) rc = dispatch_tc_hvp(pl->W, pl->pde, 0, nullptr, 0, 0, nullptr, &pl->ki);
+  else if (pl->tc) rc = dispatch_tc(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
   else
 #endif
   rc = dispatch(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
@@ -205,6 +207,7 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   pl->n_wimg = 0; pl->n_wshift = 0;
 #ifndef MPDE_EMU
   pl->n_rec = pl->n_zsp = pl->n_psmall = 0; pl->PS = 0; pl->rec_per_task = pl->zsp_per_task = 0;
+  pl->n_wimg_d = pl->n_wshift_d = pl->n_zspd = pl->n_psmall_h = 0;
   if (pl->tc) {
     pl->n_wimg = (size_t)T * (tc_image_bytes(pl->W, pl->L, mode != MODE_LOSS) / 4);
     pl->n_wshift = (size_t)T * tc::TC_MAX_L * 2;
@@ -215,18 +218,23 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
         pl->rec_seg_base[s] = off;
         const int jk = (pl->head[s] == HEAD_POISSON_DOMAIN) ? JET_LAP : (pl->head[s] == HEAD_BURGERS_DOMAIN) ? JET_XX
                      : (pl->head[s] == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
-        off += (long long)(pl->tile_begin[s + 1] - pl->tile_begin[s]) * pl->L * tc::rec_fields_points(jk) * pl->W;
+        const int rfp = (mode == MODE_HVP) ? tc::rec_fields_points_hvp(jk) : tc::rec_fields_points(jk);
+        off += (long long)(pl->tile_begin[s + 1] - pl->tile_begin[s]) * pl->L * rfp * pl->W;
       }
       pl->rec_per_task = off;
-      pl->zsp_per_task = (long long)tiles * (pl->L - 1) * 128 * pl->W;
+      pl->zsp_per_task = (long long)tiles * (pl->L - 1) * (mode == MODE_HVP ? 64 : 128) * pl->W;
       pl->PS = tc::ps_count(pl->W, pl->L, pl->OUT);
       pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS;
+      if (mode == MODE_HVP) {
+        pl->n_wimg_d = pl->n_wimg; pl->n_wshift_d = pl->n_wshift; pl->n_zspd = pl->n_zsp; pl->n_psmall_h = pl->n_psmall;
+      }
     }
   }
 #endif
   Carver c(nullptr, 0);
   c.take(pl->n_th); c.take(pl->n_thd); c.take(pl->n_scratch); c.take(pl->n_pg); c.take(pl->n_ph); c.take(pl->n_pt); c.take(pl->n_gtmp);
   c.take(pl->n_wimg); c.take(pl->n_wshift); c.take(pl->n_rec); c.take(pl->n_zsp); c.take(pl->n_psmall);
+  c.take(pl->n_wimg_d); c.take(pl->n_wshift_d); c.take(pl->n_zspd); c.take(pl->n_psmall_h);
   pl->bytes = c.off + 256;
   return MPDE_OK;
 }
@@ -267,7 +275,9 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   float* pg = c.take(pl.n_pg); float* ph = c.take(pl.n_ph); float* pt = c.take(pl.n_pt); float* gtmp = c.take(pl.n_gtmp);
   float* wimg = c.take(pl.n_wimg); float* wshift = c.take(pl.n_wshift);
   float* rec = c.take(pl.n_rec); float* zsp = c.take(pl.n_zsp); float* psmall = c.take(pl.n_psmall);
-  (void)wimg; (void)wshift; (void)rec; (void)zsp; (void)psmall;
+  float* wimg_d = c.take(pl.n_wimg_d); float* wshift_d = c.take(pl.n_wshift_d); float* zspd = c.take(pl.n_zspd);
+  float* psmall_h = c.take(pl.n_psmall_h);
+  (void)wimg; (void)wshift; (void)rec; (void)zsp; (void)psmall; (void)wimg_d; (void)wshift_d; (void)zspd; (void)psmall_h;
   if (mode != MODE_HVP) thd = nullptr;
 
   // 1. prep: theta -> theta-hat (shared theta: prepared once)
@@ -308,6 +318,11 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     rc = tc_launch_prep(pl.W, pl.L, pl.OUT, T_prep, mode != MODE_LOSS, theta, theta_stride, th, kp.th_stride, (uint8_t*)wimg,
                         (long long)tc_image_bytes(pl.W, pl.L, mode != MODE_LOSS), (int*)wshift, 2 * tc::TC_MAX_L, stream);
     if (rc) return rc;
+    if (mode == MODE_HVP) {   // the direction's image: hidden kernels of v, output layer of theta-hat-dot
+      rc = tc_launch_prep(pl.W, pl.L, pl.OUT, T_prep, 1, v, v_stride, thd, kp.thd_stride, (uint8_t*)wimg_d,
+                          (long long)tc_image_bytes(pl.W, pl.L, 1), (int*)wshift_d, 2 * tc::TC_MAX_L, stream);
+      if (rc) return rc;
+    }
   }
   cudaEvent_t prof_stop;
   const bool prof = prof_begin(mode, stream, &prof_stop);
@@ -323,6 +338,15 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     for (int s = 0; s < MAX_SEG; ++s) tp.rec_seg_base[s] = (s < pl.n_seg) ? pl.rec_seg_base[s] : 0;
     tp.zsp = zsp; tp.zsp_task_stride = pl.zsp_per_task;
     tp.psmall = psmall; tp.PS = pl.PS;
+    if (mode == MODE_HVP) {
+      tc::HvParams hp;
+      hp.t = tp;
+      hp.wimg_d = (const uint8_t*)wimg_d; hp.wimg_d_stride = tp.wimg_stride;
+      hp.wshift_d = (const int*)wshift_d; hp.wshift_d_stride = tp.wshift_stride;
+      hp.zspd = zspd; hp.psmall_h = psmall_h;
+      hp.want_grad = 1;   // the small-parameter gradient is always needed (chain rule of H v through the io scales)
+      rc = dispatch_tc_hvp(pl.W, pl.pde, 1, &hp, pl.G, T, stream, nullptr);
+    } else
     rc = dispatch_tc(pl.W, pl.pde, mode, 1, &tp, pl.G, T, stream, nullptr);
   } else
 #endif
@@ -353,6 +377,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     // hidden kernels: contraction over the task's rows from the spills; small parameters: fixed-order sum over CTAs
     tc::TcWgradParams wp;
     wp.W = pl.W; wp.L = pl.L; wp.T = T; wp.n_seg = pl.n_seg; wp.omega = net->omega;
+    wp.tile_rows = (mode == MODE_HVP) ? 64 : 128; wp.hvp_records = (mode == MODE_HVP); wp.want_hv = 0; wp.zspd = zspd;
     for (int s = 0; s <= pl.n_seg; ++s) wp.seg_tile_begin[s] = pl.tile_begin[s];
     for (int s = 0; s < pl.n_seg; ++s) {
       wp.seg_jk[s] = (pl.head[s] == HEAD_POISSON_DOMAIN) ? JET_LAP : (pl.head[s] == HEAD_BURGERS_DOMAIN) ? JET_XX
@@ -361,10 +386,19 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     }
     wp.rec = rec; wp.rec_task_stride = pl.rec_per_task; wp.zsp = zsp; wp.zsp_task_stride = pl.zsp_per_task;
     wp.gout = gout; wp.g_stride = pl.P;
-    rc = tc_launch_wgrad(&wp, stream);
-    if (rc) return rc;
+    if (mode == MODE_GRAD || want_grad) {
+      rc = tc_launch_wgrad(&wp, stream);
+      if (rc) return rc;
+    }
     rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall, gout, pl.P, stream);
     if (rc) return rc;
+    if (mode == MODE_HVP) {
+      wp.want_hv = 1; wp.gout = hv;
+      rc = tc_launch_wgrad(&wp, stream);
+      if (rc) return rc;
+      rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall_h, hv, pl.P, stream);
+      if (rc) return rc;
+    }
   } else
 #endif
   {

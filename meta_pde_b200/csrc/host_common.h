@@ -24,7 +24,8 @@ int dispatch_w256(int pde, int mode, int op, const KParams* p, int gx, int gy, v
 
 // tensor-core (tcgen05) path, widths 128 / 256 (tc_inst.cu; not part of the emulator build)
 #ifndef MPDE_EMU
-namespace tc { struct TcParams; struct TcWgradParams; }
+namespace tc { struct TcParams; struct TcWgradParams; struct HvParams; }
+int dispatch_tc_hvp(int W, int pde, int op, const tc::HvParams* p, int gx, int gy, void* stream, KernelInfo* info);
 bool tc_supported(int W, int L, int mode);
 int dispatch_tc(int W, int pde, int mode, int op, const tc::TcParams* p, int gx, int gy, void* stream, KernelInfo* info);
 size_t tc_image_bytes(int W, int L, int with_bwd);

@@ -1,0 +1,584 @@
+// tc_hvp.cuh -- tensor-core path of the Hessian-vector product (MODE_HVP): tangent-of-(forward + adjoint) of the
+// fused SIREN jet kernel (reference: the second-order pass of src/nets/maml.py:195-202).
+//
+// Same machinery as tc_pde_kernel (tc_kernels.cuh) with a tangent stream next to the primal one:
+//   forward   z    = W^T h,      zdot    = W^T hdot    + Wdot^T h
+//   reverse   abar = W zbar,     abardot = W zbardot   + Wdot zbar
+// A tile is 64 jet rows (16 points x 4 channels, or 64 value points): two B operands X (h / zbar) and Xd
+// (hdot / zbardot) of 64 KB each stay in shared memory, three accumulator sets live in TMEM (primal, W * tangent,
+// Wdot * primal: the two tangent products carry different block shifts and are added in the epilogue), and the
+// weight ring streams, per M tile, the stages of W followed by the stages of Wdot (the direction's image).
+// Spills for tc_wgrad_kernel: records (saved fields + zdot) of every layer, zbar_l and zbardot_l.
+#pragma once
+#include "tc_kernels.cuh"
+
+namespace mpde {
+namespace tc {
+
+constexpr int HR = 64;                   // jet rows per HVP tile (MMA N)
+
+template <int W> struct HvGeo {
+  static constexpr int NMT = W / 128, KSL = W / 64, NEPI = W, NT = W + 64;
+  static constexpr int SLAB = HR * 128;                 // [64 rows][64 k] fp16
+  static constexpr int XBYTES = 2 * KSL * SLAB;         // hi slabs then lo slabs (one operand)
+  static constexpr int RING = NSTAGE * STAGE_BYTES;
+  // misc: xs[2][HR], ybuf[HR][2], ydbuf[HR][2], red[HR] f32; cmax[2][8] u32; terms[4] f32; barriers; tmem slot
+  static constexpr int MISC = 2 * HR * 4 + 2 * HR * 4 + 2 * HR * 4 + HR * 4 + 64 + 16 + (2 * NSTAGE + 3) * 8 + 16;
+  static constexpr int SMEM = 2 * XBYTES + RING + MISC;
+  static constexpr int TMEM_COLS = 512;                 // 3 accumulator sets x NMT x 64 columns (<= 384)
+  static constexpr int D0 = 0, D1 = NMT * HR, D2 = 2 * NMT * HR;   // primal, W*tangent, Wdot*primal
+};
+
+template <int W> struct HvCtx {
+  typedef HvGeo<W> G;
+  uint8_t* xbuf; uint8_t* xdbuf; uint8_t* ring;
+  float* xs; float* ybuf; float* ydbuf; float* red; uint32_t* cmax; float* terms;
+  uint64_t* full; uint64_t* empty; uint64_t* xready; uint64_t* dfull;
+  uint32_t* tmem_slot;
+  TC_DEV void carve() {
+    uint8_t* s = tc_smem_raw;
+    xbuf = s; xdbuf = s + G::XBYTES; ring = s + 2 * G::XBYTES;
+    xs = reinterpret_cast<float*>(ring + G::RING);
+    ybuf = xs + 2 * HR; ydbuf = ybuf + 2 * HR; red = ydbuf + 2 * HR;
+    cmax = reinterpret_cast<uint32_t*>(red + HR);
+    terms = reinterpret_cast<float*>(cmax + 16);
+    full = reinterpret_cast<uint64_t*>(terms + 4);
+    empty = full + NSTAGE; xready = empty + NSTAGE; dfull = xready + 1;
+    tmem_slot = reinterpret_cast<uint32_t*>(dfull + 2);
+  }
+};
+
+
+// ---------------------------------------------------------------------------------------------------------
+template <int W, int HEAD>
+struct HvTile {
+  typedef HvGeo<W> G;
+  typedef HeadTraits<HEAD> HT;
+  static constexpr int JK = HT::JK, OUT = HT::OUT;
+  typedef JetTraits<JK> JT;
+  static constexpr int C = JT::C, NF = JT::NF, NFT = JT::NF + JT::C;
+  static constexpr bool VAL = (JK == JET_V);
+  static constexpr int CP = VAL ? 1 : 4;
+  static constexpr int PTS = HR / CP;
+
+  static TC_DEV uint32_t xoff(int r, int n) {
+    return (uint32_t)(n >> 6) * G::SLAB + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u +
+           ((((uint32_t)(n & 63) >> 3) ^ (uint32_t)(r & 7)) << 4) + (uint32_t)(n & 7) * 2u;
+  }
+  static TC_DEV void store_x(uint8_t* xb, int r, int n, float y) {
+    __half h, l;
+    split_f16(y, h, l);
+    const uint32_t o = xoff(r, n);
+    *reinterpret_cast<__half*>(xb + o) = h;
+    *reinterpret_cast<__half*>(xb + G::KSL * G::SLAB + o) = l;
+  }
+  // bounds of |a_c| and |adot_c| from the pre-activation jets (no sincos)
+  static TC_DEV void bound_update(float om, const float* z, const float* zd, float (&bnd)[8]) {
+    const float o2 = om * om;
+    bnd[4] = fmaxf(bnd[4], om * fabsf(zd[0]));
+    if (!VAL) {
+      const float avd = fabsf(zd[0]);
+      bnd[1] = fmaxf(bnd[1], om * fabsf(z[1]));
+      bnd[2] = fmaxf(bnd[2], om * fabsf(z[2]));
+      bnd[5] = fmaxf(bnd[5], om * fabsf(zd[1]) + o2 * fabsf(z[1]) * avd);
+      bnd[6] = fmaxf(bnd[6], om * fabsf(zd[2]) + o2 * fabsf(z[2]) * avd);
+      if (JT::Q) {
+        float pp = 0.f, ppd = 0.f;
+        if (JT::D0) { pp += z[1] * z[1]; ppd += fabsf(z[1] * zd[1]); }
+        if (JT::D1) { pp += z[2] * z[2]; ppd += fabsf(z[2] * zd[2]); }
+        bnd[3] = fmaxf(bnd[3], om * fabsf(z[3]) + o2 * pp);
+        bnd[7] = fmaxf(bnd[7], om * fabsf(zd[3]) + o2 * fabsf(z[3]) * avd + 2.f * o2 * ppd + o2 * om * pp * avd);
+      }
+    }
+  }
+  // fold the 8 bounds, barrier, read the shifts.  FWD: the primal value channel is |sin| <= 1.
+  template <bool FWD>
+  static TC_DEV void agree_shifts(HvCtx<W>& cx, int& seq, const float (&bnd)[8], int (&sh)[8], int tid, int lane) {
+    uint32_t* cm = cx.cmax + (seq & 1) * 8;
+    MPDE_UNROLL
+    for (int c = 0; c < 8; ++c) {
+      const bool used = VAL ? (c == 4 || (!FWD && c == 0)) : ((c & 3) < C && !(FWD && c == 0));
+      if (used) fold_max(cm + c, bnd[c], lane);
+    }
+    epi_sync<G::NEPI>();
+    MPDE_UNROLL
+    for (int c = 0; c < 8; ++c) sh[c] = shift_for_max(__uint_as_float(cm[c]));
+    if (FWD) sh[0] = 14;
+    if (tid == 0) {
+      uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 8;
+      MPDE_UNROLL
+      for (int c = 0; c < 8; ++c) other[c] = 0u;
+    }
+    ++seq;
+  }
+
+  // ---- the epilogue side of one tile (all W epilogue threads) ------------------------------------------
+  static TC_DEV void run(const HvParams& hp, HvCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile,
+                         uint32_t tbase, int& seq, uint32_t& dpar, const int* wshift, const int* wshift_d) {
+    const TcParams& p = hp.t;
+    const KParams& kp = p.k;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = tid, mt = n >> 7;
+    const float om = kp.omega;
+    const int L = kp.L;
+    const float* th = kp.th + (size_t)task * kp.th_stride;
+    const float* thd = kp.thd + (size_t)task * kp.thd_stride;
+    const float* prm = kp.prm + (size_t)task * kp.nprm;
+    const int pt0 = tile * PTS;
+    const float* pts = sg.pts + (size_t)task * sg.task_stride;
+    const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * HR);
+    float* xs = cx.xs;
+    float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W + n;
+    constexpr int PPC = 16 / CP;                        // points per 16-column chunk
+
+    for (int i = tid; i < PTS; i += G::NEPI) {
+      const int gp = pt0 + i;
+      float x0 = 0.f, x1 = 0.f;
+      if (gp < sg.n) { x0 = pts[2 * (size_t)gp]; x1 = pts[2 * (size_t)gp + 1]; }
+      xs[i] = x0; xs[HR + i] = x1;
+    }
+    // ---- layer 0 ----
+    int sh[8];
+    {
+      const float w00 = mpde_ldg(th + n), w01 = mpde_ldg(th + W + n), b0 = mpde_ldg(th + 2 * W + n);
+      const float d00 = mpde_ldg(thd + n), d01 = mpde_ldg(thd + W + n), db0 = mpde_ldg(thd + 2 * W + n);
+      epi_sync<G::NEPI>();                              // xs visible
+      float bnd[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int pl = 0; pl < PTS; ++pl) {
+        const float z[4] = {0.f, w00, w01, 0.f};
+        const float zd[4] = {fmaf(d00, xs[pl], fmaf(d01, xs[HR + pl], db0)), d00, d01, 0.f};
+        bound_update(om, z, zd, bnd);
+      }
+      agree_shifts<true>(cx, seq, bnd, sh, tid, lane);
+      float ys[8];
+      for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
+      MPDE_NOUNROLL
+      for (int pl = 0; pl < PTS; ++pl) {
+        float z[4], zd[4], a[4], ad[4], sv[5];
+        z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[HR + pl], b0)); z[1] = w00; z[2] = w01; z[3] = 0.f;
+        zd[0] = fmaf(d00, xs[pl], fmaf(d01, xs[HR + pl], db0)); zd[1] = d00; zd[2] = d01; zd[3] = 0.f;
+        jet_act_fwd<JK>(om, z, a, sv);
+        jet_act_tan<JK>(om, sv, zd, ad);
+        MPDE_UNROLL
+        for (int f = 0; f < NF; ++f) recp[(size_t)(f * PTS + pl) * W] = sv[f];
+        MPDE_UNROLL
+        for (int c = 0; c < C; ++c) recp[(size_t)((NF + c) * PTS + pl) * W] = zd[c];
+        MPDE_UNROLL
+        for (int c = 0; c < CP; ++c) {
+          store_x(cx.xbuf, CP * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
+          store_x(cx.xdbuf, CP * pl + c, n, c < C ? ad[c] * ys[4 + c] : 0.f);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    mbar_arrive(cx.xready);
+
+    // ---- hidden layers ----
+    for (int l = 1; l < L; ++l) {
+      const float bias = mpde_ldg(th + ph_off_layer(W, l) + 2 * W * W + n);
+      const float biasd = mpde_ldg(thd + ph_off_layer(W, l) + 2 * W * W + n);
+      float zs[4], zs1[4], zs2[4];
+      {
+        const int sw = wshift[l], swd = wshift_d[l];
+        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
+      }
+      mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+      tc_fence_after();
+      float bnd[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < HR / 16; ++ch) {
+        uint32_t v0[16], v1[16], v2[16];
+        tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+        tmem_ld_wait();
+        MPDE_UNROLL
+        for (int q = 0; q < PPC; ++q) {
+          float z[4] = {0.f, 0.f, 0.f, 0.f}, zd[4] = {0.f, 0.f, 0.f, 0.f};
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) {
+            z[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
+            zd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
+          }
+          zd[0] += biasd;
+          bound_update(om, z, zd, bnd);
+        }
+      }
+      agree_shifts<true>(cx, seq, bnd, sh, tid, lane);   // barrier: all MMAs of this layer completed
+      float ys[8];
+      for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < HR / 16; ++ch) {
+        uint32_t v0[16], v1[16], v2[16];
+        tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+        tmem_ld_wait();
+        MPDE_UNROLL
+        for (int q = 0; q < PPC; ++q) {
+          const int pl = ch * PPC + q;
+          float z[4] = {0.f, 0.f, 0.f, 0.f}, zd[4] = {0.f, 0.f, 0.f, 0.f}, a[4], ad[4], sv[5];
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) {
+            z[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
+            zd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
+          }
+          z[0] += bias; zd[0] += biasd;
+          jet_act_fwd<JK>(om, z, a, sv);
+          jet_act_tan<JK>(om, sv, zd, ad);
+          MPDE_UNROLL
+          for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f) * PTS + pl) * W] = sv[f];
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c) * PTS + pl) * W] = zd[c];
+          MPDE_UNROLL
+          for (int c = 0; c < CP; ++c) {
+            store_x(cx.xbuf, CP * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
+            store_x(cx.xdbuf, CP * pl + c, n, c < C ? ad[c] * ys[4 + c] : 0.f);
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(cx.xready);
+    }
+
+    // ---- output layer: lanes 0..OUT-1 of the first M tile hold y, ydot ----
+    if (mt == 0) {
+      mbar_wait(&cx.dfull[0], dpar); dpar ^= 1u;
+      tc_fence_after();
+      if (warp == 0) {
+        float zs[4], zs1[4], zs2[4];
+        {
+          const int sw = wshift[L], swd = wshift_d[L];
+          for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
+        }
+        MPDE_NOUNROLL
+        for (int ch = 0; ch < HR / 16; ++ch) {
+          uint32_t v0[16], v1[16], v2[16];
+          tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+          tmem_ld_wait();
+          if (lane < OUT) {
+            MPDE_UNROLL
+            for (int q = 0; q < 16; ++q) {
+              const int c = VAL ? 0 : (q & 3);
+              cx.ybuf[(ch * 16 + q) * 2 + lane] = __uint_as_float(v0[q]) * zs[c];
+              cx.ydbuf[(ch * 16 + q) * 2 + lane] = fmaf(__uint_as_float(v1[q]), zs1[c], __uint_as_float(v2[q]) * zs2[c]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+    }
+    epi_sync<G::NEPI>();
+
+    // ---- head: value, seeds ybar and their tangents ybardot ----
+    if (tid < PTS) {
+      const int pl = tid;
+      const float* bL = th + ph_off_out(W, L) + W * OUT;
+      const float* bLd = thd + ph_off_out(W, L) + W * OUT;
+      float u[OUT * C], ud[OUT * C], ub[OUT * C], ubd[OUT * C];
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o)
+        MPDE_UNROLL
+        for (int c = 0; c < C; ++c) {
+          float y = cx.ybuf[(CP * pl + c) * 2 + o], yd = cx.ydbuf[(CP * pl + c) * 2 + o];
+          if (c == 0) { y += mpde_ldg(bL + o); yd += mpde_ldg(bLd + o); }
+          u[o * C + c] = y; ud[o * C + c] = yd;
+        }
+      const bool valid = (pt0 + pl) < sg.n;
+      float res = 0.f;
+      float val = head_eval<HEAD>(u, xs[pl], xs[HR + pl], prm, sg.coef, ub, &res);
+      head_tangent<HEAD>(u, ud, xs[pl], xs[HR + pl], prm, sg.coef, ubd);
+      if (!valid) val = 0.f;
+      cx.red[pl] = val;
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o)
+        MPDE_UNROLL
+        for (int c = 0; c < CP; ++c) {
+          cx.ybuf[(CP * pl + c) * 2 + o] = (valid && c < C) ? ub[o * C + c] : 0.f;
+          cx.ydbuf[(CP * pl + c) * 2 + o] = (valid && c < C) ? ubd[o * C + c] : 0.f;
+        }
+    }
+    epi_sync<G::NEPI>();
+    if (warp == 0) {
+      float s = 0.f;
+      MPDE_UNROLL
+      for (int j = 0; j < (PTS + 31) / 32; ++j) s += (lane + 32 * j < PTS) ? cx.red[lane + 32 * j] : 0.f;
+      MPDE_UNROLL
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) cx.terms[seg_id] += s;
+    }
+
+    // ==================== reverse pass and its tangent ====================
+    const bool wg = hp.want_grad != 0;
+    float* psg = p.psmall + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
+    float* psh = hp.psmall_h + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
+    const size_t zoff = (size_t)task * p.zsp_task_stride + (size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) * HR * W + n;
+    float* zsp_tile = p.zsp + zoff;
+    float* zspd_tile = hp.zspd + zoff;
+    float wl[OUT], wld[OUT];
+    MPDE_UNROLL
+    for (int o = 0; o < OUT; ++o) {
+      wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
+      wld[o] = mpde_ldg(thd + ph_off_out(W, L) + n * OUT + o);
+    }
+    if (tid < OUT) {
+      float g = 0.f, h = 0.f;
+      for (int pl = 0; pl < PTS; ++pl) { g += cx.ybuf[(CP * pl) * 2 + tid]; h += cx.ydbuf[(CP * pl) * 2 + tid]; }
+      psh[ps_off_wl(W, L) + W * OUT + tid] += h;
+      if (wg) psg[ps_off_wl(W, L) + W * OUT + tid] += g;
+    }
+    int shz[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int l = L - 1; l >= 0; --l) {
+      float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f}, zs2[4] = {0.f, 0.f, 0.f, 0.f};
+      if (l < L - 1) {
+        const int sw = wshift[l + 1], swd = wshift_d[l + 1];
+        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-shz[c] - sw); zs1[c] = pow2i(-shz[4 + c] - sw); zs2[c] = pow2i(-shz[c] - swd); }
+        mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+        tc_fence_after();
+      }
+      float bnd[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      float bsum = 0.f, bsumd = 0.f, g0 = 0.f, g1 = 0.f, h0 = 0.f, h1 = 0.f, gw[OUT], hw[OUT];
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o) { gw[o] = 0.f; hw[o] = 0.f; }
+      float* zl = zsp_tile + (size_t)(l - 1) * HR * W;       // only dereferenced for l >= 1
+      float* zld = zspd_tile + (size_t)(l - 1) * HR * W;
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < HR / 16; ++ch) {
+        uint32_t v0[16], v1[16], v2[16];
+        if (l < L - 1) {
+          tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+          tmem_ld_wait();
+        }
+        MPDE_UNROLL
+        for (int q = 0; q < PPC; ++q) {
+          const int pl = ch * PPC + q;
+          float ab[4] = {0.f, 0.f, 0.f, 0.f}, abd[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zd[4] = {0.f, 0.f, 0.f, 0.f};
+          float zb[4] = {0.f, 0.f, 0.f, 0.f}, zbd[4] = {0.f, 0.f, 0.f, 0.f};
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) {
+            if (l < L - 1) {
+              ab[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
+              abd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
+            } else {
+              float a_ = 0.f, ad_ = 0.f;
+              MPDE_UNROLL
+              for (int o = 0; o < OUT; ++o) {
+                const float yb = cx.ybuf[(CP * pl + c) * 2 + o], ybd = cx.ydbuf[(CP * pl + c) * 2 + o];
+                a_ = fmaf(wl[o], yb, a_);
+                ad_ = fmaf(wl[o], ybd, fmaf(wld[o], yb, ad_));
+              }
+              ab[c] = a_; abd[c] = ad_;
+            }
+          }
+          MPDE_UNROLL
+          for (int f = 0; f < NF; ++f) sv[f] = recp[(size_t)((l * NFT + f) * PTS + pl) * W];
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) zd[c] = recp[(size_t)((l * NFT + NF + c) * PTS + pl) * W];
+          jet_act_bwd<JK>(om, sv, ab, zb);
+          jet_act_bwd_tan<JK>(om, sv, zd, ab, abd, zbd);
+          bsum += zb[0]; bsumd += zbd[0];
+          if (l == L - 1) {
+            float a[4], ad[4];
+            jet_act_from_saved<JK>(om, sv, a);
+            jet_act_tan<JK>(om, sv, zd, ad);
+            MPDE_UNROLL
+            for (int o = 0; o < OUT; ++o)
+              MPDE_UNROLL
+              for (int c = 0; c < C; ++c) {
+                const float yb = cx.ybuf[(CP * pl + c) * 2 + o], ybd = cx.ydbuf[(CP * pl + c) * 2 + o];
+                gw[o] = fmaf(a[c], yb, gw[o]);
+                hw[o] = fmaf(ad[c], yb, fmaf(a[c], ybd, hw[o]));
+              }
+          }
+          if (l == 0) {
+            if (VAL) {
+              g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[HR + pl], zb[0], g1);
+              h0 = fmaf(xs[pl], zbd[0], h0); h1 = fmaf(xs[HR + pl], zbd[0], h1);
+            } else {
+              g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[HR + pl], zb[0], zb[2]);
+              h0 += fmaf(xs[pl], zbd[0], zbd[1]); h1 += fmaf(xs[HR + pl], zbd[0], zbd[2]);
+            }
+          } else {
+            MPDE_UNROLL
+            for (int c = 0; c < CP; ++c) {
+              const float z_ = c < C ? zb[c] : 0.f, zd_ = c < C ? zbd[c] : 0.f;
+              zl[(size_t)(CP * pl + c) * W] = z_;
+              zld[(size_t)(CP * pl + c) * W] = zd_;
+              bnd[c] = fmaxf(bnd[c], fabsf(z_));
+              bnd[4 + c] = fmaxf(bnd[4 + c], fabsf(zd_));
+            }
+          }
+        }
+      }
+      psh[ps_off_bias(W, l) + n] += bsumd;
+      if (wg) psg[ps_off_bias(W, l) + n] += bsum;
+      if (l == L - 1) {
+        MPDE_UNROLL
+        for (int o = 0; o < OUT; ++o) {
+          psh[ps_off_wl(W, L) + n * OUT + o] += hw[o];
+          if (wg) psg[ps_off_wl(W, L) + n * OUT + o] += gw[o];
+        }
+      }
+      if (l == 0) {
+        psh[n] += h0; psh[W + n] += h1;
+        if (wg) { psg[n] += g0; psg[W + n] += g1; }
+        epi_sync<G::NEPI>();                              // xs / ybuf are rewritten by the next tile
+        break;
+      }
+      agree_shifts<false>(cx, seq, bnd, shz, tid, lane);  // barrier: all adjoint MMAs that read X / Xd completed
+      float ys[8];
+      for (int c = 0; c < 8; ++c) ys[c] = pow2i(shz[c]);
+      MPDE_NOUNROLL
+      for (int r0 = 0; r0 < HR; r0 += 8) {
+        float zv[8], zdv[8];
+        MPDE_UNROLL
+        for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)(r0 + j) * W]; zdv[j] = zld[(size_t)(r0 + j) * W]; }
+        MPDE_UNROLL
+        for (int j = 0; j < 8; ++j) {
+          const int c = VAL ? 0 : (j & 3);
+          store_x(cx.xbuf, r0 + j, n, zv[j] * ys[c]);
+          store_x(cx.xdbuf, r0 + j, n, zdv[j] * ys[4 + c]);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(cx.xready);
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// kernel: grid = (ctas_per_task, T)
+// ---------------------------------------------------------------------------------------------------------
+template <int W, int PDE>
+__global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_constant__ HvParams hp) {
+  typedef HvGeo<W> G;
+  HvCtx<W> cx;
+  cx.carve();
+  const TcParams& p = hp.t;
+  const KParams& kp = p.k;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int task = blockIdx.y;
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  const int L = kp.L;
+  const int n_tiles = kp.seg_tile_begin[kp.n_seg];
+
+  if (tid == 0) {
+    if (smem_u32(tc_smem_raw) & 1023u) { printf("tc_hvp_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
+    for (int i = 0; i < NSTAGE; ++i) { mbar_init(&cx.full[i], 1); mbar_init(&cx.empty[i], 1); }
+    mbar_init(cx.xready, G::NEPI);
+    mbar_init(&cx.dfull[0], 1); mbar_init(&cx.dfull[1], 1);
+    mbar_fence_init();
+    for (int i = 0; i < 16; ++i) cx.cmax[i] = 0u;
+    for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
+  }
+  if (warp == 0) tmem_alloc(cx.tmem_slot, G::TMEM_COLS);
+  {
+    float* psg = p.psmall + (size_t)cta * p.PS;
+    float* psh = hp.psmall_h + (size_t)cta * p.PS;
+    for (int i = tid; i < p.PS; i += G::NT) { psh[i] = 0.f; if (hp.want_grad) psg[i] = 0.f; }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = *cx.tmem_slot;
+  constexpr int PER = G::NMT * G::KSL;                       // stages per hidden layer (per image)
+  const int nst_fwd = (L - 1) * PER + G::KSL;
+  const int nsteps = 2 * L - 1;                              // L-1 hidden, output, L-1 adjoint contractions
+
+  if (warp < G::NEPI / 32) {
+    int seq = 0; uint32_t dpar = 0;
+    const int* wshift = p.wshift + (size_t)task * p.wshift_stride;
+    const int* wshift_d = hp.wshift_d + (size_t)task * hp.wshift_d_stride;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      int s = 0;
+      while (s + 1 < kp.n_seg && t >= kp.seg_tile_begin[s + 1]) ++s;
+      const int tile = t - kp.seg_tile_begin[s];
+      const SegDesc& sg = kp.seg[s];
+      if (PDE == PDE_POISSON) {
+        if (sg.head == HEAD_POISSON_DOMAIN) HvTile<W, HEAD_POISSON_DOMAIN>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+        else HvTile<W, HEAD_POISSON_BOUNDARY>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+      } else if (PDE == PDE_BURGERS) {
+        if (sg.head == HEAD_BURGERS_DOMAIN) HvTile<W, HEAD_BURGERS_DOMAIN>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+        else HvTile<W, HEAD_BURGERS_IC>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+      } else {
+        if (sg.head == HEAD_HYPER_DOMAIN) HvTile<W, HEAD_HYPER_DOMAIN>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+        else if (sg.head == HEAD_HYPER_TOP) HvTile<W, HEAD_HYPER_TOP>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+        else HvTile<W, HEAD_HYPER_BOTTOM>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
+      }
+    }
+  } else if (warp == G::NEPI / 32) {
+    // ===== producer: per contraction and M tile, the stages of W then the stages of Wdot =====
+    if (lane == 0) {
+      const uint8_t* img = p.wimg + (size_t)task * p.wimg_stride;
+      const uint8_t* imgd = hp.wimg_d + (size_t)task * hp.wimg_d_stride;
+      uint32_t stage = 0, phase = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int step = 1; step <= nsteps; ++step) {
+          const int nmt = (step != L) ? G::NMT : 1;
+          // first stage of this contraction in the image: hidden layer `step`, output layer, adjoint copies (L-1 .. 1)
+          const int base = (step < L) ? (step - 1) * PER : (step == L ? (L - 1) * PER : nst_fwd + (step - L - 1) * PER);
+          for (int mt = 0; mt < nmt; ++mt)
+            for (int which = 0; which < 2; ++which)
+              for (int s = 0; s < G::KSL; ++s) {
+                const uint8_t* src = (which ? imgd : img) + (size_t)(base + mt * G::KSL + s) * STAGE_BYTES;
+                mbar_wait(&cx.empty[stage], phase ^ 1u);
+                mbar_arrive_expect_tx(&cx.full[stage], STAGE_BYTES);
+                bulk_g2s(cx.ring + (size_t)stage * STAGE_BYTES, src, STAGE_BYTES, &cx.full[stage]);
+                if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
+              }
+        }
+      }
+    }
+  } else {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 0);
+      const uint32_t xb = smem_u32(cx.xbuf), xdb = smem_u32(cx.xdbuf);
+      uint32_t stage = 0, phase = 0, xpar = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int step = 1; step <= nsteps; ++step) {
+          mbar_wait(cx.xready, xpar); xpar ^= 1u;
+          tc_fence_after();
+          const int nmt = (step != L) ? G::NMT : 1;
+          for (int mt = 0; mt < nmt; ++mt) {
+            const uint32_t d0 = tbase + G::D0 + (uint32_t)mt * HR, d1 = tbase + G::D1 + (uint32_t)mt * HR,
+                           d2 = tbase + G::D2 + (uint32_t)mt * HR;
+            for (int which = 0; which < 2; ++which) {
+              uint32_t acc = 0;
+              for (int s = 0; s < G::KSL; ++s) {
+                mbar_wait(&cx.full[stage], phase);
+                tc_fence_after();
+                const uint32_t a_hi = smem_u32(cx.ring + (size_t)stage * STAGE_BYTES), a_lo = a_hi + 16384u;
+                const uint32_t b_hi = xb + (uint32_t)s * G::SLAB, b_lo = b_hi + (uint32_t)G::KSL * G::SLAB;
+                const uint32_t c_hi = xdb + (uint32_t)s * G::SLAB, c_lo = c_hi + (uint32_t)G::KSL * G::SLAB;
+                MPDE_UNROLL
+                for (int kk = 0; kk < 4; ++kk) {
+                  const uint64_t ah = desc_kmajor(a_hi + kk * 32), al = desc_kmajor(a_lo + kk * 32);
+                  const uint64_t bh = desc_kmajor(b_hi + kk * 32), bl = desc_kmajor(b_lo + kk * 32);
+                  if (which == 0) {
+                    const uint64_t ch = desc_kmajor(c_hi + kk * 32), cl = desc_kmajor(c_lo + kk * 32);
+                    mma_f16_ss(d0, ah, bh, idesc, acc); mma_f16_ss(d0, al, bh, idesc, 1); mma_f16_ss(d0, ah, bl, idesc, 1);   // W * primal
+                    mma_f16_ss(d1, ah, ch, idesc, acc); mma_f16_ss(d1, al, ch, idesc, 1); mma_f16_ss(d1, ah, cl, idesc, 1);   // W * tangent
+                  } else {
+                    mma_f16_ss(d2, ah, bh, idesc, acc); mma_f16_ss(d2, al, bh, idesc, 1); mma_f16_ss(d2, ah, bl, idesc, 1);   // Wdot * primal
+                  }
+                  acc = 1;
+                }
+                tc_commit(&cx.empty[stage]);
+                if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
+              }
+            }
+            tc_commit(&cx.dfull[mt]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 0) tmem_dealloc(tbase, G::TMEM_COLS);
+  if (tid < MAX_SEG) kp.partial_terms[(size_t)cta * MAX_SEG + tid] = cx.terms[tid];
+}
+
+}  // namespace tc
+}  // namespace mpde

@@ -2,6 +2,7 @@
 #include "host_common.h"
 #include "tc_kernels.cuh"
 #include "tc_wgrad.cuh"
+#include "tc_hvp.cuh"
 #include <mutex>
 
 namespace mpde {
@@ -46,9 +47,40 @@ static int tc_run_width(int pde, int mode, int op, const TcParams* p, int gx, in
   return 1;
 }
 
+template <int W, int PDE>
+static int tc_run_hvp_inst(int op, const HvParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  typedef HvGeo<W> G;
+  auto kfn = tc_hvp_kernel<W, PDE>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&]() { attr_err = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM); });
+  if (attr_err != cudaSuccess) return 4;
+  if (op == 0) {
+    info->nt = G::NT; info->smem = G::SMEM; info->occ = 1; info->np = HR / 4;
+    return 0;
+  }
+  g_launches++;
+  kfn<<<dim3(gx, gy, 1), dim3(G::NT, 1, 1), G::SMEM, (cudaStream_t)stream>>>(*p);
+  return cudaGetLastError() != cudaSuccess ? 4 : 0;
+}
+template <int W>
+static int tc_run_hvp_width(int pde, int op, const HvParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  switch (pde) {
+    case PDE_POISSON: return tc_run_hvp_inst<W, PDE_POISSON>(op, p, gx, gy, stream, info);
+    case PDE_BURGERS: return tc_run_hvp_inst<W, PDE_BURGERS>(op, p, gx, gy, stream, info);
+    case PDE_HYPER:   return tc_run_hvp_inst<W, PDE_HYPER>(op, p, gx, gy, stream, info);
+  }
+  return 1;
+}
+int dispatch_tc_hvp(int W, int pde, int op, const HvParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  if (W == 128) return tc_run_hvp_width<128>(pde, op, p, gx, gy, stream, info);
+  if (W == 256) return tc_run_hvp_width<256>(pde, op, p, gx, gy, stream, info);
+  return 1;
+}
+
 // modes the tensor-core path implements for this width / depth (the FP32-FMA kernels serve everything else)
 bool tc_supported(int W, int L, int mode) {
-  return (W == 128 || W == 256) && L >= 2 && L <= TC_MAX_L && (mode == MODE_LOSS || mode == MODE_GRAD);
+  return (W == 128 || W == 256) && L >= 2 && L <= TC_MAX_L && (mode == MODE_LOSS || mode == MODE_GRAD || mode == MODE_HVP);
 }
 
 int dispatch_tc(int W, int pde, int mode, int op, const TcParams* p, int gx, int gy, void* stream, KernelInfo* info) {

@@ -29,17 +29,33 @@ MPDE_HD int ps_off_wl(int W, int L) { return (L + 2) * W; }
 MPDE_HD int ps_count(int W, int L, int OUT) { return (L + 2) * W + W * OUT + OUT; }
 // floats of activation records per (tile, layer): NF * PTS * W
 MPDE_HD int rec_fields_points(int jk) { return jk == JET_V ? 2 * 128 : (jk == JET_G ? 4 * 32 : 5 * 32); }
+// HVP tiles (64 rows): saved fields + the tangent pre-activations zdot
+MPDE_HD int rec_fields_points_hvp(int jk) { return jk == JET_V ? 3 * 64 : (jk == JET_G ? 7 * 16 : 9 * 16); }
 
 
 struct TcWgradParams {
   int W, L, T, n_seg;
   float omega;
+  int tile_rows;                            // jet rows per spilled tile: 128 (GRAD spills) or 64 (HVP spills)
+  int hvp_records;                          // records carry the tangent pre-activations zdot after the NF saved fields
+  int want_hv;                              // 0: grad W_l = h^T zbar;  1: (H v)_W_l = hdot^T zbar + h^T zbardot
   int seg_tile_begin[MAX_SEG + 1];
   int seg_jk[MAX_SEG];
   long long rec_seg_base[MAX_SEG];
   const float* rec; long long rec_task_stride;
-  const float* zsp; long long zsp_task_stride;
+  const float* zsp; long long zsp_task_stride;     // zbar_l
+  const float* zspd;                               // zbardot_l (HVP spills), same layout and stride
   float* gout; long long g_stride;          // [T][P] natural layout; hidden kernels are written (not accumulated)
+};
+
+struct HvParams {
+  TcParams t;                      // primal: segments, theta-hat, W image + shifts, records, zbar spill, small partials (grad)
+  const uint8_t* wimg_d;           // direction image (same layout as t.wimg, built from v / theta-hat-dot)
+  long long wimg_d_stride;
+  const int* wshift_d; long long wshift_d_stride;
+  float* zspd;                     // zbardot spill (layout of t.zsp)
+  float* psmall_h;                 // [T][G][PS] per-CTA partials of (H v) on the small parameters
+  int want_grad;                   // also accumulate the small-parameter gradient into t.psmall
 };
 
 }  // namespace tc

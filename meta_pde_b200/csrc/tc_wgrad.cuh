@@ -1,22 +1,26 @@
-// tc_wgrad.cuh -- hidden-layer weight gradients of the tensor-core path.
+// tc_wgrad.cuh -- hidden-layer weight gradients (and Hessian-vector products) of the tensor-core path.
 //
-//   grad W_l [k][n] = sum over the task's jet rows r of  h_{l-1}[r][k] * zbar_l[r][n]        
+//   grad W_l [k][n]   = sum over the task's jet rows r of  h_{l-1}[r][k] * zbar_l[r][n]                 
+//   (H v)_W_l [k][n]  = sum_r  hdot_{l-1}[r][k] * zbar_l[r][n] + h_{l-1}[r][k] * zbardot_l[r][n]
 //
-// tc_pde_kernel (GRAD) spills the activation records of every layer and zbar_l in fp32; this kernel is the
-// contraction over rows: one CTA per (task, layer, 128-wide k tile) keeps the [128 x W] fp32 result in tensor memory
-// for the whole task (fixed summation order: deterministic), recomputes h_{l-1} from the records, splits both operands
-// into tf32 hi/lo on the fly (x = hi + lo, hi = x with the low 13 mantissa bits cleared) and issues the three
-// kind::tf32 MMAs hi*hi + lo*hi + hi*lo.  The converters write both operands K-major (slab row = neuron, the 128 bytes
-// run over 32 jet rows): kind::tf32 with MN-major 128B-swizzled operands returned zeros on B200 (tools/tc_probe.cu).
-// No scaling is needed (tf32 has the fp32 exponent), so tiles of very different magnitude accumulate exactly.
+// tc_pde_kernel / tc_hvp_kernel spill the activation records of every layer and zbar_l (zbardot_l) in fp32; this
+// kernel is the contraction over rows.  One CTA per (task, layer, 128-wide k tile) walks the task's rows in steps of
+// 32: 256 converter threads recompute h (hdot) from the records, split both operands into tf32 hi/lo
+// (round-to-nearest, x = hi + lo) and write them K-major into a two-slot shared-memory pipeline (slab row = neuron,
+// the 128 bytes run over the 32 rows; kind::tf32 with MN-major swizzled operands returned zeros on B200,
+// tools/tc_probe.cu); one thread issues the three kind::tf32 MMAs hi*hi + lo*hi + hi*lo per 8 rows.  tf32 keeps the
+// fp32 exponent, so rows of very different magnitude need no scaling.
+//
+// The tensor core's accumulator is trusted for 4 steps only (48 accumulations): its additions are not
+// round-to-nearest and a sum over all rows of a task drifted by 3e-4 at 16k points (measured).  Every 4 steps the
+// converter threads add the TMEM accumulator into an fp32 master copy in registers (two TMEM buffers alternate).
+// Fixed summation order: deterministic.
 #pragma once
 #include "tc_kernels.cuh"
 
 namespace mpde {
 namespace tc {
 
-// x = hi + lo, both exactly representable in tf32 (round-to-nearest split: the dropped lo*lo term and the residual
-// of lo are unbiased; a truncating split leaves a systematic error of the sign of the product)
 TC_DEV float tf32_rn(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -24,7 +28,8 @@ TC_DEV float tf32_rn(float x) {
 }
 TC_DEV void split_tf32(float x, float& hi, float& lo) { hi = tf32_rn(x); lo = tf32_rn(x - hi); }
 
-constexpr int WG_QR = 32;                    // rows per pipeline step (a quarter tile)
+constexpr int WG_QR = 32;                    // rows per pipeline step
+constexpr int WG_GROUP = 4;                  // steps per accumulator generation
 
 template <int W> struct WgGeo {
   static constexpr int NMT = W / 128;
@@ -33,6 +38,81 @@ template <int W> struct WgGeo {
   static constexpr int NCONV = 256, NT = NCONV + 32;
   static constexpr int SMEM = 2 * SLOT + 96;
 };
+
+// 16-byte chunk `chunk` (4 consecutive rows) of slab row `row`, swizzled
+TC_DEV uint32_t wg_chunk_off(int row, int chunk) {
+  return (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u + (((uint32_t)chunk ^ (uint32_t)(row & 7)) << 4);
+}
+TC_DEV void wg_store4(uint8_t* hi_base, uint8_t* lo_base, uint32_t off, const float (&x)[4]) {
+  float hi[4], lo[4];
+  MPDE_UNROLL
+  for (int i = 0; i < 4; ++i) split_tf32(x[i], hi[i], lo[i]);
+  *reinterpret_cast<float4*>(hi_base + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+  *reinterpret_cast<float4*>(lo_base + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+// B operand: 32 rows x W of zbar (or zbardot), fp32 [row][n] contiguous -> slab row n, chunk = group of 4 rows.
+// All loads are issued before the first conversion.
+template <int W>
+TC_DEV void wg_convert_z(const float* zq, uint8_t* z_hi, uint8_t* z_lo, int tid) {
+  constexpr int NIT = W * (WG_QR / 4) / 256;
+  float x[NIT][4];
+  MPDE_UNROLL
+  for (int j = 0; j < NIT; ++j) {
+    const int idx = tid + 256 * j, nn = idx % W, g = idx / W;
+    MPDE_UNROLL
+    for (int i = 0; i < 4; ++i) x[j][i] = zq[(size_t)(4 * g + i) * W + nn];
+  }
+  MPDE_UNROLL
+  for (int j = 0; j < NIT; ++j) {
+    const int idx = tid + 256 * j, nn = idx % W, g = idx / W;
+    wg_store4(z_hi, z_lo, wg_chunk_off(nn, g), x[j]);
+  }
+}
+
+// A operand: h (TAN = false) or hdot (TAN = true) of 32 rows x 128 neurons, recomputed from the records
+// [field][point][W]; this thread: neuron k (slab row), every other chunk starting at `half`.
+template <int JK, bool TAN, bool HVPREC>
+TC_DEV void wg_convert_h(const float* rp, int W, int PTS, int p0, float om, uint8_t* h_hi, uint8_t* h_lo, int k, int half) {
+  typedef JetTraits<JK> JT;
+  constexpr int NF = JT::NF, C = JT::C;
+  if (JK == JET_V) {
+    // 32 points = 32 rows; chunk g = points 4g..4g+3.  h = S (field 0); hdot = om * Cc * zdot (fields 1, NF)
+    float s0[4][4], s1[4][4];
+    MPDE_UNROLL
+    for (int j = 0; j < 4; ++j)
+      MPDE_UNROLL
+      for (int i = 0; i < 4; ++i) {
+        const int pl = p0 + 4 * (half + 2 * j) + i;
+        s0[j][i] = rp[(size_t)((TAN ? 1 : 0) * PTS + pl) * W];
+        if (TAN) s1[j][i] = rp[(size_t)(NF * PTS + pl) * W];
+      }
+    MPDE_UNROLL
+    for (int j = 0; j < 4; ++j) {
+      float x[4];
+      MPDE_UNROLL
+      for (int i = 0; i < 4; ++i) x[i] = TAN ? om * s0[j][i] * s1[j][i] : s0[j][i];
+      wg_store4(h_hi, h_lo, wg_chunk_off(k, half + 2 * j), x);
+    }
+  } else {
+    // 8 points; chunk pq = the 4 channel rows of point pq
+    constexpr int NL = NF + ((TAN && HVPREC) ? C : 0);
+    float f[4][NL];
+    MPDE_UNROLL
+    for (int j = 0; j < 4; ++j) {
+      const int pl = p0 + half + 2 * j;
+      MPDE_UNROLL
+      for (int q = 0; q < NL; ++q) f[j][q] = rp[(size_t)(q * PTS + pl) * W];
+    }
+    MPDE_UNROLL
+    for (int j = 0; j < 4; ++j) {
+      float a[4] = {0.f, 0.f, 0.f, 0.f};
+      if (TAN) jet_act_tan<JK>(om, f[j], f[j] + NF, a);
+      else jet_act_from_saved<JK>(om, f[j], a);
+      wg_store4(h_hi, h_lo, wg_chunk_off(k, half + 2 * j), a);
+    }
+  }
+}
 
 template <int W>
 __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_constant__ TcWgradParams p) {
@@ -45,6 +125,9 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
   const int l = 1 + blockIdx.x / G::NMT, kt = blockIdx.x % G::NMT;
   const int L = p.L;
   const int n_tiles = p.seg_tile_begin[p.n_seg];
+  const int qpt = p.tile_rows / WG_QR;                 // 32-row quarters per tile
+  const int npair = p.want_hv ? 2 : 1;
+  const int nsteps = n_tiles * qpt * npair;
   if (tid == 0) {
     if (smem_u32(smem) & 1023u) { printf("tc_wgrad_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     mbar_init(&bars[0], G::NCONV); mbar_init(&bars[1], G::NCONV);
@@ -58,22 +141,18 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = *tmem_slot;
-  const int nq = n_tiles * (TR / WG_QR);
 
   if (warp < G::NCONV / 32) {
-    // ===== converters: global fp32 -> tf32 hi/lo slabs =====
+    // ===== converters =====
     const float* rec_t = p.rec + (size_t)task * p.rec_task_stride;
-    const float* zsp_t = p.zsp + (size_t)task * p.zsp_task_stride;
     const int k = tid & 127, half = tid >> 7;
-    // fp32 master copy of this thread's part of the result: TMEM lane 32 * (warp & 3) + lane, W/2 columns.  The tensor
-    // core's own accumulator is only trusted for one tile (48 accumulation steps): its additions are not
-    // round-to-nearest, and a sum over all rows of a task drifted by 3e-4 at 16k points (measured).
+    // fp32 master copy of this thread's part of the result: TMEM lane 32 * (warp & 3) + lane, W/2 columns
     float master[W / 2];
     MPDE_UNROLL
     for (int j = 0; j < W / 2; ++j) master[j] = 0.f;
-    auto promote = [&](int tt) {
-      const int b = tt & 1;
-      mbar_wait(&bars[4 + b], (tt >> 1) & 1);
+    auto promote = [&](int gen) {
+      const int b = gen & 1;
+      mbar_wait(&bars[4 + b], (gen >> 1) & 1);
       tc_fence_after();
       MPDE_UNROLL
       for (int c = 0; c < W / 2; c += 32) {
@@ -86,78 +165,49 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
       tc_fence_before();
       mbar_arrive(&bars[6 + b]);
     };
-    for (int q = 0; q < nq; ++q) {
-      const int slot = q & 1;
-      if ((q & 3) == 0 && q >= 4) promote(q / 4 - 1);
-      if (q >= 2) mbar_wait(&bars[2 + slot], ((q >> 1) - 1) & 1);
+    for (int st = 0; st < nsteps; ++st) {
+      const int slot = st & 1;
+      if ((st % WG_GROUP) == 0 && st >= WG_GROUP) promote(st / WG_GROUP - 1);
+      if (st >= 2) mbar_wait(&bars[2 + slot], ((st >> 1) - 1) & 1);
       uint8_t* h_hi = smem + (size_t)slot * G::SLOT;
       uint8_t* h_lo = h_hi + G::HBYTES;
       uint8_t* z_hi = h_lo + G::HBYTES;
       uint8_t* z_lo = z_hi + G::ZBYTES;
-      const int t = q / (TR / WG_QR), qq = q % (TR / WG_QR);
+      const int pair = st % npair, q = st / npair;
+      const int t = q / qpt, qq = q % qpt;
       int s = 0;
       while (s + 1 < p.n_seg && t >= p.seg_tile_begin[s + 1]) ++s;
       const int jk = p.seg_jk[s];
       const int tile = t - p.seg_tile_begin[s];
-      // zbar quarter [32 rows][W] fp32 -> B operand, K-major: slab row = output neuron n, the 128 bytes run over the
-      // 32 rows r.  A thread takes one n and four consecutive r (four coalesced loads, one 16-byte store).
+      // pair 0 of an H v product: (hdot, zbar); pair 1: (h, zbardot); gradient: (h, zbar)
+      const bool tan = p.want_hv && pair == 0;
+      const float* zsrc = (p.want_hv && pair == 1) ? p.zspd : p.zsp;
+      const float* zq = zsrc + (size_t)task * p.zsp_task_stride + ((size_t)t * (L - 1) + (l - 1)) * p.tile_rows * W +
+                        (size_t)qq * WG_QR * W;
+      wg_convert_z<W>(zq, z_hi, z_lo, tid);
       {
-        const float* zq = zsp_t + ((size_t)t * (L - 1) + (l - 1)) * TR * W + (size_t)qq * WG_QR * W;
-        MPDE_UNROLL
-        for (int j = 0; j < W * (WG_QR / 4) / G::NCONV; ++j) {
-          const int idx = tid + G::NCONV * j;
-          const int nn = idx % W, g = idx / W;                 // g: group of 4 rows
-          float x[4], hi[4], lo[4];
-          MPDE_UNROLL
-          for (int i = 0; i < 4; ++i) x[i] = zq[(size_t)(4 * g + i) * W + nn];
-          MPDE_UNROLL
-          for (int i = 0; i < 4; ++i) split_tf32(x[i], hi[i], lo[i]);
-          const uint32_t off = (uint32_t)(nn >> 3) * 1024u + (uint32_t)(nn & 7) * 128u + (((uint32_t)g ^ (uint32_t)(nn & 7)) << 4);
-          *reinterpret_cast<float4*>(z_hi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-          *reinterpret_cast<float4*>(z_lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-        }
-      }
-      // h_{l-1} quarter, neurons kt*128 .. +128, recomputed from the records of layer l-1 -> A operand, K-major:
-      // slab row = input neuron k, the 128 bytes run over the 32 rows r (4 channels of a point = one 16-byte chunk)
-      {
+        const int CP = jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, p0 = qq * (WG_QR / CP);
         const int NF = jk == JET_V ? 2 : (jk == JET_G ? 4 : 5);
-        const int CP = jk == JET_V ? 1 : 4, PTS = TR / CP, PPQ = WG_QR / CP;
-        const float* rp = rec_t + p.rec_seg_base[s] + ((size_t)tile * L + (l - 1)) * (size_t)(NF * PTS) * W + kt * 128 + k;
-        const uint32_t rowoff = (uint32_t)(k >> 3) * 1024u + (uint32_t)(k & 7) * 128u;
-        if (jk == JET_V) {
-          // 32 points = 32 rows: this thread's half takes the chunks g = half, half + 2, ... (4 points each)
-          for (int g = half; g < WG_QR / 4; g += 2) {
-            float x[4], hi[4], lo[4];
-            MPDE_UNROLL
-            for (int i = 0; i < 4; ++i) x[i] = rp[(size_t)(qq * PPQ + 4 * g + i) * W];
-            MPDE_UNROLL
-            for (int i = 0; i < 4; ++i) split_tf32(x[i], hi[i], lo[i]);
-            const uint32_t off = rowoff + (((uint32_t)g ^ (uint32_t)(k & 7)) << 4);
-            *reinterpret_cast<float4*>(h_hi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-            *reinterpret_cast<float4*>(h_lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-          }
+        const int NFT = NF + (p.hvp_records ? (jk == JET_V ? 1 : (jk == JET_G ? 3 : 4)) : 0);
+        const float* rp = rec_t + p.rec_seg_base[s] + ((size_t)tile * L + (l - 1)) * (size_t)(NFT * PTS) * W + kt * 128 + k;
+        const float om = p.omega;
+        if (!tan) {
+          if (jk == JET_V) wg_convert_h<JET_V, false, false>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
+          else if (jk == JET_G) wg_convert_h<JET_G, false, false>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
+          else if (jk == JET_LAP) wg_convert_h<JET_LAP, false, false>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
+          else wg_convert_h<JET_XX, false, false>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
         } else {
-          for (int pq = half; pq < PPQ; pq += 2) {           // one point = rows 4 pq .. 4 pq + 3 = chunk pq
-            const int pl = qq * PPQ + pq;
-            float a[4] = {0.f, 0.f, 0.f, 0.f}, hi[4], lo[4];
-            float sv[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-            for (int f = 0; f < NF; ++f) sv[f] = rp[(size_t)(f * PTS + pl) * W];
-            if (jk == JET_G) jet_act_from_saved<JET_G>(p.omega, sv, a);
-            else if (jk == JET_LAP) jet_act_from_saved<JET_LAP>(p.omega, sv, a);
-            else jet_act_from_saved<JET_XX>(p.omega, sv, a);
-            MPDE_UNROLL
-            for (int i = 0; i < 4; ++i) split_tf32(a[i], hi[i], lo[i]);
-            const uint32_t off = rowoff + (((uint32_t)pq ^ (uint32_t)(k & 7)) << 4);
-            *reinterpret_cast<float4*>(h_hi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-            *reinterpret_cast<float4*>(h_lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-          }
+          if (jk == JET_V) wg_convert_h<JET_V, true, true>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
+          else if (jk == JET_G) wg_convert_h<JET_G, true, true>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
+          else if (jk == JET_LAP) wg_convert_h<JET_LAP, true, true>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
+          else wg_convert_h<JET_XX, true, true>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
         }
       }
       fence_proxy_async_smem();
       mbar_arrive(&bars[slot]);
     }
-    // ===== last tile, then the result: [128 k][W n] -> grad W_l =====
-    promote(n_tiles - 1);
+    // ===== last generation, then the result: [128 k][W n] -> grad W_l =====
+    promote((nsteps - 1) / WG_GROUP);
     float* out = p.gout + (size_t)task * p.g_stride + nat_off_layer(W, l) + (size_t)(kt * 128 + 32 * (warp & 3) + lane) * W +
                  (warp >> 2) * (W / 2);
     MPDE_UNROLL
@@ -166,13 +216,13 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(FMT_TF32, 128, W, 0, 0);
-      for (int q = 0; q < nq; ++q) {
-        const int slot = q & 1;
-        const int tt = q >> 2, b = tt & 1;              // tile and its accumulator buffer
+      for (int st = 0; st < nsteps; ++st) {
+        const int slot = st & 1;
+        const int gen = st / WG_GROUP, b = gen & 1;     // accumulator generation and its TMEM buffer
         const uint32_t d = tbase + (uint32_t)(b * W);
-        uint32_t acc = (q & 3) ? 1u : 0u;               // a fresh accumulator per tile
-        if ((q & 3) == 0 && tt >= 2) { mbar_wait(&bars[6 + b], ((tt >> 1) - 1) & 1); tc_fence_after(); }
-        mbar_wait(&bars[slot], (q >> 1) & 1);
+        uint32_t acc = (st % WG_GROUP) ? 1u : 0u;       // a fresh accumulator per generation
+        if ((st % WG_GROUP) == 0 && gen >= 2) { mbar_wait(&bars[6 + b], ((gen >> 1) - 1) & 1); tc_fence_after(); }
+        mbar_wait(&bars[slot], (st >> 1) & 1);
         tc_fence_after();
         const uint32_t h_hi = smem_u32(smem + (size_t)slot * G::SLOT), h_lo = h_hi + G::HBYTES;
         const uint32_t z_hi = h_lo + G::HBYTES, z_lo = z_hi + G::ZBYTES;
@@ -185,7 +235,7 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
           mma_tf32_ss(d, ah, bl, idesc, 1);
         }
         tc_commit(&bars[2 + slot]);
-        if ((q & 3) == 3) tc_commit(&bars[4 + b]);
+        if ((st % WG_GROUP) == WG_GROUP - 1 || st == nsteps - 1) tc_commit(&bars[4 + b]);
       }
     }
   }
