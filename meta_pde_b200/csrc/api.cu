@@ -205,9 +205,9 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   pl->n_pt = ctas * MAX_SEG;
   pl->n_gtmp = need_gtmp ? (size_t)T * pl->P : 0;
   pl->n_wimg = 0; pl->n_wshift = 0;
-#ifndef MPDE_EMU
   pl->n_rec = pl->n_zsp = pl->n_psmall = 0; pl->PS = 0; pl->rec_per_task = pl->zsp_per_task = 0;
   pl->n_wimg_d = pl->n_wshift_d = pl->n_zspd = pl->n_psmall_h = 0;
+#ifndef MPDE_EMU
   if (pl->tc) {
     pl->n_wimg = (size_t)T * (tc_image_bytes(pl->W, pl->L, mode != MODE_LOSS) / 4);
     pl->n_wshift = (size_t)T * tc::TC_MAX_L * 2;
