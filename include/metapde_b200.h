@@ -207,7 +207,8 @@ const char* mpde_backend(void);
  * every launch of the jet kernel is bracketed by a cudaEvent pair on the caller's stream (events
  * are created on first use: do not enable inside a CUDA-graph capture).  mpde_prof_read
  * synchronises on the recorded events of `mode` (mpde_mode), returns their summed duration in
- * milliseconds and their count, and clears them. */
+ * milliseconds and their count, and clears them.  mode 3 = the tensor-core path's weight-gradient
+ * contraction kernel (tc_wgrad_kernel), all launches of GRAD and HVP evaluations together. */
 int mpde_prof_enable(int on);
 int mpde_prof_read(int mode, double* total_ms, int64_t* launches);
 

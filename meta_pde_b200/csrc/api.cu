@@ -37,8 +37,8 @@ int device_sm_count() {
 struct ProfState {
   std::mutex mu;
   bool on = false;
-  std::vector<cudaEvent_t> ev[3];   // pairs: [2i] start, [2i+1] stop
-  size_t used[3] = {0, 0, 0};
+  std::vector<cudaEvent_t> ev[4];   // pairs: [2i] start, [2i+1] stop; slot 3 = tc_wgrad_kernel launches
+  size_t used[4] = {0, 0, 0, 0};
 };
 static ProfState g_prof;
 static bool prof_begin(int mode, void* stream, cudaEvent_t* stop) {
@@ -387,14 +387,18 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     wp.rec = rec; wp.rec_task_stride = pl.rec_per_task; wp.zsp = zsp; wp.zsp_task_stride = pl.zsp_per_task;
     wp.gout = gout; wp.g_stride = pl.P;
     if (mode == MODE_GRAD || want_grad) {
+      cudaEvent_t ws; const bool wprof = prof_begin(3, stream, &ws);
       rc = tc_launch_wgrad(&wp, stream);
+      if (wprof) cudaEventRecord(ws, (cudaStream_t)stream);
       if (rc) return rc;
     }
     rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall, gout, pl.P, stream);
     if (rc) return rc;
     if (mode == MODE_HVP) {
       wp.want_hv = 1; wp.gout = hv;
+      cudaEvent_t ws; const bool wprof = prof_begin(3, stream, &ws);
       rc = tc_launch_wgrad(&wp, stream);
+      if (wprof) cudaEventRecord(ws, (cudaStream_t)stream);
       if (rc) return rc;
       rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall_h, hv, pl.P, stream);
       if (rc) return rc;
@@ -462,14 +466,14 @@ int mpde_prof_enable(int on) {
 #ifndef MPDE_EMU
   std::lock_guard<std::mutex> lk(g_prof.mu);
   g_prof.on = on != 0;
-  if (on) for (int m = 0; m < 3; ++m) g_prof.used[m] = 0;
+  if (on) for (int m = 0; m < 4; ++m) g_prof.used[m] = 0;
 #else
   (void)on;
 #endif
   return MPDE_OK;
 }
 int mpde_prof_read(int mode, double* total_ms, int64_t* launches) {
-  if (mode < 0 || mode > 2 || !total_ms || !launches) return MPDE_INVALID_ARG;
+  if (mode < 0 || mode > 3 || !total_ms || !launches) return MPDE_INVALID_ARG;
   *total_ms = 0.0; *launches = 0;
 #ifndef MPDE_EMU
   std::lock_guard<std::mutex> lk(g_prof.mu);
