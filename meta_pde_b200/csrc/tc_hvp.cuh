@@ -343,6 +343,13 @@ struct HvTile {
       MPDE_NOUNROLL
       for (int ch = 0; ch < HR / 16; ++ch) {
         uint32_t v0[16], v1[16], v2[16];
+        // all record loads of the chunk are issued before its first spill store and before the accumulator fetch
+        // (see tc_kernels.cuh: the compiler cannot hoist a load above the previous point's stores)
+        float svb[PPC][NF + C];
+        MPDE_UNROLL
+        for (int q = 0; q < PPC; ++q)
+          MPDE_UNROLL
+          for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f) * PTS + ch * PPC + q) * W];
         if (l < L - 1) {
           tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
           tmem_ld_wait();
@@ -369,9 +376,9 @@ struct HvTile {
             }
           }
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) sv[f] = recp[(size_t)((l * NFT + f) * PTS + pl) * W];
+          for (int f = 0; f < NF; ++f) sv[f] = svb[q][f];
           MPDE_UNROLL
-          for (int c = 0; c < C; ++c) zd[c] = recp[(size_t)((l * NFT + NF + c) * PTS + pl) * W];
+          for (int c = 0; c < C; ++c) zd[c] = svb[q][NF + c];
           jet_act_bwd<JK>(om, sv, ab, zb);
           jet_act_bwd_tan<JK>(om, sv, zd, ab, abd, zbd);
           bsum += zb[0]; bsumd += zbd[0];

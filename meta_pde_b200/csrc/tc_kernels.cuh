@@ -447,10 +447,22 @@ struct TcTile {
       MPDE_NOUNROLL
       for (int ch = 0; ch < TR / 32; ++ch) {
         uint32_t v[32];
-        if (l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
         constexpr int PPC = 32 / CP;                      // points per 32-row chunk
+        constexpr int SB = VAL ? 16 : 8;                  // points per batch of record loads
         MPDE_UNROLL
-        for (int q = 0; q < PPC; ++q) {
+        for (int q0 = 0; q0 < PPC; q0 += SB) {
+        // All record loads of the batch are issued before anything is stored (the compiler cannot move a load above
+        // the zbar spill stores of the previous point: one exposed memory latency per point, ncu r01e) and before
+        // the accumulator chunk is fetched from tensor memory.
+        float svb[SB][NF];
+        MPDE_UNROLL
+        for (int qq = 0; qq < SB; ++qq)
+          MPDE_UNROLL
+          for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f) * PTS + ch * PPC + q0 + qq) * W];
+        if (q0 == 0 && l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
+        MPDE_UNROLL
+        for (int qq = 0; qq < SB; ++qq) {
+          const int q = q0 + qq;
           const int pl = ch * PPC + q;
           float ab[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zb[4] = {0.f, 0.f, 0.f, 0.f};
           MPDE_UNROLL
@@ -465,7 +477,7 @@ struct TcTile {
             }
           }
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) sv[f] = recp[(size_t)((l * NF + f) * PTS + pl) * W];
+          for (int f = 0; f < NF; ++f) sv[f] = svb[qq][f];
           jet_act_bwd<JK>(om, sv, ab, zb);
           bsum += zb[0];
           if (l == L - 1) {
@@ -487,6 +499,7 @@ struct TcTile {
               bnd[c] = fmaxf(bnd[c], fabsf(z_));
             }
           }
+        }
         }
       }
       // small-parameter gradients: owner-computes read-modify-write into this CTA's partial

@@ -35,7 +35,7 @@ template <int W> struct WgGeo {
   static constexpr int NMT = W / 128;
   static constexpr int HBYTES = 128 * 128, ZBYTES = W * 128;  // one K-major slab each: [128 k][32 r], [W n][32 r] tf32
   static constexpr int SLOT = 2 * (HBYTES + ZBYTES);          // hi + lo of both operands
-  static constexpr int NCONV = 256, NT = NCONV + 32;
+  static constexpr int NGRP = 2, NCONV = 256 * NGRP, NT = NCONV + 32;   // converter groups alternate pipeline steps
   static constexpr int SMEM = 2 * SLOT + 96;
 };
 
@@ -52,20 +52,22 @@ TC_DEV void wg_store4(uint8_t* hi_base, uint8_t* lo_base, uint32_t off, const fl
 }
 
 // B operand: 32 rows x W of zbar (or zbardot), fp32 [row][n] contiguous -> slab row n, chunk = group of 4 rows.
-// All loads are issued before the first conversion.
-template <int W>
-TC_DEV void wg_convert_z(const float* zq, uint8_t* z_hi, uint8_t* z_lo, int tid) {
-  constexpr int NIT = W * (WG_QR / 4) / 256;
-  float x[NIT][4];
+// Iterations [J0, J0 + NJ) of the group's 256 threads; loads and stores are separate calls so that the caller can
+// keep several batches of loads in flight.
+template <int W, int J0, int NJ>
+TC_DEV void wg_load_z(const float* zq, int tid, float (&x)[NJ][4]) {
   MPDE_UNROLL
-  for (int j = 0; j < NIT; ++j) {
-    const int idx = tid + 256 * j, nn = idx % W, g = idx / W;
+  for (int j = 0; j < NJ; ++j) {
+    const int idx = tid + 256 * (J0 + j), nn = idx % W, g = idx / W;
     MPDE_UNROLL
     for (int i = 0; i < 4; ++i) x[j][i] = zq[(size_t)(4 * g + i) * W + nn];
   }
+}
+template <int W, int J0, int NJ>
+TC_DEV void wg_store_z(uint8_t* z_hi, uint8_t* z_lo, int tid, const float (&x)[NJ][4]) {
   MPDE_UNROLL
-  for (int j = 0; j < NIT; ++j) {
-    const int idx = tid + 256 * j, nn = idx % W, g = idx / W;
+  for (int j = 0; j < NJ; ++j) {
+    const int idx = tid + 256 * (J0 + j), nn = idx % W, g = idx / W;
     wg_store4(z_hi, z_lo, wg_chunk_off(nn, g), x[j]);
   }
 }
@@ -130,7 +132,7 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
   const int nsteps = n_tiles * qpt * npair;
   if (tid == 0) {
     if (smem_u32(smem) & 1023u) { printf("tc_wgrad_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
-    mbar_init(&bars[0], G::NCONV); mbar_init(&bars[1], G::NCONV);
+    mbar_init(&bars[0], 256); mbar_init(&bars[1], 256);
     mbar_init(&bars[2], 1); mbar_init(&bars[3], 1);
     mbar_init(&bars[4], 1); mbar_init(&bars[5], 1);
     mbar_init(&bars[6], G::NCONV); mbar_init(&bars[7], G::NCONV);
@@ -143,21 +145,23 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
   const uint32_t tbase = *tmem_slot;
 
   if (warp < G::NCONV / 32) {
-    // ===== converters =====
+    // ===== converters: group g (8 warps) fills pipeline slot g on steps st = g, g + 2, ... =====
     const float* rec_t = p.rec + (size_t)task * p.rec_task_stride;
-    const int k = tid & 127, half = tid >> 7;
-    // fp32 master copy of this thread's part of the result: TMEM lane 32 * (warp & 3) + lane, W/2 columns
-    float master[W / 2];
+    const int grp = warp >> 3, gtid = tid & 255;
+    const int k = gtid & 127, half = gtid >> 7;
+    // fp32 master copy of this thread's part of the result: TMEM lane 32 * (warp & 3) + lane, W/4 columns
+    constexpr int MC = W / 4;
+    float master[MC];
     MPDE_UNROLL
-    for (int j = 0; j < W / 2; ++j) master[j] = 0.f;
+    for (int j = 0; j < MC; ++j) master[j] = 0.f;
     auto promote = [&](int gen) {
       const int b = gen & 1;
       mbar_wait(&bars[4 + b], (gen >> 1) & 1);
       tc_fence_after();
       MPDE_UNROLL
-      for (int c = 0; c < W / 2; c += 32) {
+      for (int c = 0; c < MC; c += 32) {
         uint32_t v[32];
-        tmem_ld32(tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)(b * W + (warp >> 2) * (W / 2) + c)), v);
+        tmem_ld32(tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)(b * W + (warp >> 2) * MC + c)), v);
         tmem_ld_wait();
         MPDE_UNROLL
         for (int j = 0; j < 32; ++j) master[c + j] += __uint_as_float(v[j]);
@@ -165,10 +169,9 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
       tc_fence_before();
       mbar_arrive(&bars[6 + b]);
     };
-    for (int st = 0; st < nsteps; ++st) {
+    int done_gen = 0;                                   // generations 0 .. done_gen-1 are in the master copy
+    for (int st = grp; st < nsteps; st += G::NGRP) {
       const int slot = st & 1;
-      if ((st % WG_GROUP) == 0 && st >= WG_GROUP) promote(st / WG_GROUP - 1);
-      if (st >= 2) mbar_wait(&bars[2 + slot], ((st >> 1) - 1) & 1);
       uint8_t* h_hi = smem + (size_t)slot * G::SLOT;
       uint8_t* h_lo = h_hi + G::HBYTES;
       uint8_t* z_hi = h_lo + G::HBYTES;
@@ -184,7 +187,15 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
       const float* zsrc = (p.want_hv && pair == 1) ? p.zspd : p.zsp;
       const float* zq = zsrc + (size_t)task * p.zsp_task_stride + ((size_t)t * (L - 1) + (l - 1)) * p.tile_rows * W +
                         (size_t)qq * WG_QR * W;
-      wg_convert_z<W>(zq, z_hi, z_lo, tid);
+      // all z loads are in flight while the h records are loaded and converted
+      constexpr int NIT = W * (WG_QR / 4) / 256, NJA = NIT / 2, NJB = NIT - NJA;
+      float zA[NJA][4], zB[NJB][4];
+      wg_load_z<W, 0, NJA>(zq, gtid, zA);
+      wg_load_z<W, NJA, NJB>(zq, gtid, zB);
+      // Promotion lags the MMAs by two steps (no pipeline drain at a generation boundary); the slot is only needed
+      // for the stores, so the z loads above are already in flight while this thread waits.
+      while (st >= 2 && done_gen < (st - 2) / WG_GROUP) promote(done_gen++);
+      if (st >= 2) mbar_wait(&bars[2 + slot], ((st >> 1) - 1) & 1);
       {
         const int CP = jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, p0 = qq * (WG_QR / CP);
         const int NF = jk == JET_V ? 2 : (jk == JET_G ? 4 : 5);
@@ -203,15 +214,17 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
           else wg_convert_h<JET_XX, true, true>(rp, W, PTS, p0, om, h_hi, h_lo, k, half);
         }
       }
+      wg_store_z<W, 0, NJA>(z_hi, z_lo, gtid, zA);
+      wg_store_z<W, NJA, NJB>(z_hi, z_lo, gtid, zB);
       fence_proxy_async_smem();
       mbar_arrive(&bars[slot]);
     }
-    // ===== last generation, then the result: [128 k][W n] -> grad W_l =====
-    promote((nsteps - 1) / WG_GROUP);
+    // ===== remaining generations, then the result: [128 k][W n] -> grad W_l =====
+    while (done_gen <= (nsteps - 1) / WG_GROUP) promote(done_gen++);
     float* out = p.gout + (size_t)task * p.g_stride + nat_off_layer(W, l) + (size_t)(kt * 128 + 32 * (warp & 3) + lane) * W +
-                 (warp >> 2) * (W / 2);
+                 (warp >> 2) * MC;
     MPDE_UNROLL
-    for (int j = 0; j < W / 2; ++j) out[j] = master[j];   // gout rows are only 4-byte aligned (P is odd-ish)
+    for (int j = 0; j < MC; ++j) out[j] = master[j];   // gout rows are only 4-byte aligned (P is odd-ish)
   } else {
     // ===== MMA issuer =====
     if (lane == 0) {

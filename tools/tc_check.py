@@ -47,15 +47,21 @@ def timing(modes=("loss",)):
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             reps = 5
+            K.prof_enable(True)
             e0.record()
             for _ in range(reps):
                 out = fn()
             e1.record()
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
+            mid = {"loss": 0, "grad": 1, "hvp": 2}[mode]
+            main_ms, main_n = K.prof_read(mid)
+            wg_ms, wg_n = K.prof_read(3)
+            K.prof_enable(False)
             print(json.dumps({"W": W, "L": L, "T": T, "n": n, "mode": mode, "tc": os.environ.get("MPDE_DISABLE_TC") != "1",
                               "ms": round(ms, 3), "alg_tflops": round(mult * Pw * rows * T / ms * 1e-9, 2),
-                              "loss0": float(out[0][0])}), flush=True)
+                              "main_kernel_ms": round(main_ms / max(main_n, 1), 3), "wgrad_ms_per_launch": round(wg_ms / max(wg_n, 1), 3),
+                              "wgrad_launches_per_call": wg_n / reps, "loss0": float(out[0][0])}), flush=True)
 
 
 if __name__ == "__main__":
