@@ -128,7 +128,8 @@ struct HvTile {
     const float* pts = sg.pts + (size_t)task * sg.task_stride;
     const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * HR);
     float* xs = cx.xs;
-    float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W + n;
+    float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W +
+             (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
     constexpr int PPC = 16 / CP;                        // points per 16-column chunk
 
     for (int i = tid; i < PTS; i += G::NEPI) {
@@ -160,9 +161,9 @@ struct HvTile {
         jet_act_fwd<JK>(om, z, a, sv);
         jet_act_tan<JK>(om, sv, zd, ad);
         MPDE_UNROLL
-        for (int f = 0; f < NF; ++f) recp[(size_t)(f * PTS + pl) * W] = sv[f];
+        for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
         MPDE_UNROLL
-        for (int c = 0; c < C; ++c) recp[(size_t)((NF + c) * PTS + pl) * W] = zd[c];
+        for (int c = 0; c < C; ++c) recp[(size_t)((NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
         MPDE_UNROLL
         for (int c = 0; c < CP; ++c) {
           store_x(cx.xbuf, CP * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
@@ -224,9 +225,9 @@ struct HvTile {
           jet_act_fwd<JK>(om, z, a, sv);
           jet_act_tan<JK>(om, sv, zd, ad);
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f) * PTS + pl) * W] = sv[f];
+          for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f)) * (PTS * W) + (pl) * 128] = sv[f];
           MPDE_UNROLL
-          for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c) * PTS + pl) * W] = zd[c];
+          for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
           MPDE_UNROLL
           for (int c = 0; c < CP; ++c) {
             store_x(cx.xbuf, CP * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
@@ -349,7 +350,7 @@ struct HvTile {
         MPDE_UNROLL
         for (int q = 0; q < PPC; ++q)
           MPDE_UNROLL
-          for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f) * PTS + ch * PPC + q) * W];
+          for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + (ch * PPC + q) * 128];
         if (l < L - 1) {
           tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
           tmem_ld_wait();
@@ -433,16 +434,29 @@ struct HvTile {
       agree_shifts<false>(cx, seq, bnd, shz, tid, lane);  // barrier: all adjoint MMAs that read X / Xd completed
       float ys[8];
       for (int c = 0; c < 8; ++c) ys[c] = pow2i(shz[c]);
+      // zbar_l / zbardot_l back from the spills (L2): the next batch of 8 rows is in flight while this one is stored
+      float zv[8], zdv[8], zv2[8], zdv2[8];
+      MPDE_UNROLL
+      for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)j * W]; zdv[j] = zld[(size_t)j * W]; }
       MPDE_NOUNROLL
-      for (int r0 = 0; r0 < HR; r0 += 8) {
-        float zv[8], zdv[8];
+      for (int r0 = 0; r0 < HR; r0 += 16) {
         MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)(r0 + j) * W]; zdv[j] = zld[(size_t)(r0 + j) * W]; }
+        for (int j = 0; j < 8; ++j) { zv2[j] = zl[(size_t)(r0 + 8 + j) * W]; zdv2[j] = zld[(size_t)(r0 + 8 + j) * W]; }
         MPDE_UNROLL
         for (int j = 0; j < 8; ++j) {
           const int c = VAL ? 0 : (j & 3);
           store_x(cx.xbuf, r0 + j, n, zv[j] * ys[c]);
           store_x(cx.xdbuf, r0 + j, n, zdv[j] * ys[4 + c]);
+        }
+        if (r0 + 16 < HR) {
+          MPDE_UNROLL
+          for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)(r0 + 16 + j) * W]; zdv[j] = zld[(size_t)(r0 + 16 + j) * W]; }
+        }
+        MPDE_UNROLL
+        for (int j = 0; j < 8; ++j) {
+          const int c = VAL ? 0 : (j & 3);
+          store_x(cx.xbuf, r0 + 8 + j, n, zv2[j] * ys[c]);
+          store_x(cx.xdbuf, r0 + 8 + j, n, zdv2[j] * ys[4 + c]);
         }
       }
       fence_proxy_async_smem();

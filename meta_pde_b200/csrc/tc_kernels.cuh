@@ -238,7 +238,8 @@ struct TcTile {
     // activation records of this tile: [layer][field][point][neuron]
     float* recp = nullptr;
     if (MODE != MODE_LOSS)
-      recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NF * PTS) * W + n;
+      recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NF * PTS) * W +
+             (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
 
     // ---- points ----
     for (int i = tid; i < PTS; i += G::NEPI) {
@@ -264,7 +265,7 @@ struct TcTile {
         jet_act_fwd<JK>(om, z, a, sv);
         if (MODE != MODE_LOSS) {
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) recp[(size_t)(f * PTS + pl) * W] = sv[f];
+          for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
         }
         if (VAL) {
           store_x(cx.xbuf, pl, n, a[0] * ys[0]);
@@ -319,7 +320,7 @@ struct TcTile {
             jet_act_fwd<JK>(om, z, a, sv);
             if (MODE != MODE_LOSS) {
               MPDE_UNROLL
-              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f) * PTS + ch * 32 + q) * W] = sv[f];
+              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (ch * 32 + q) * 128] = sv[f];
             }
             store_x(cx.xbuf, ch * 32 + q, n, a[0] * ys[0]);
           }
@@ -333,7 +334,7 @@ struct TcTile {
             jet_act_fwd<JK>(om, z, a, sv);
             if (MODE != MODE_LOSS) {
               MPDE_UNROLL
-              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f) * PTS + ch * 8 + q) * W] = sv[f];
+              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (ch * 8 + q) * 128] = sv[f];
             }
             MPDE_UNROLL
             for (int c = 0; c < 4; ++c) store_x(cx.xbuf, ch * 32 + 4 * q + c, n, c < C ? a[c] * ys[c] : 0.f);
@@ -458,7 +459,7 @@ struct TcTile {
         MPDE_UNROLL
         for (int qq = 0; qq < SB; ++qq)
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f) * PTS + ch * PPC + q0 + qq) * W];
+          for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (ch * PPC + q0 + qq) * 128];
         if (q0 == 0 && l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
         MPDE_UNROLL
         for (int qq = 0; qq < SB; ++qq) {
@@ -513,13 +514,22 @@ struct TcTile {
       agree_shifts<true>(cx, l, seq, bnd, shz, tid, lane);      // barrier: all adjoint MMAs that read X have completed
       float ys[4];
       for (int c = 0; c < 4; ++c) ys[c] = pow2i(shz[c]);
+      // zbar_l back from the spill (L2), two batches of 8 rows in flight
+      float za[8], zb2[8];
+      MPDE_UNROLL
+      for (int j = 0; j < 8; ++j) za[j] = zl[(size_t)j * W];
       MPDE_NOUNROLL
-      for (int r0 = 0; r0 < TR; r0 += 8) {
-        float zv[8];
+      for (int r0 = 0; r0 < TR; r0 += 16) {
         MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) zv[j] = zl[(size_t)(r0 + j) * W];
+        for (int j = 0; j < 8; ++j) zb2[j] = zl[(size_t)(r0 + 8 + j) * W];
         MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) store_x(cx.xbuf, r0 + j, n, zv[j] * ys[VAL ? 0 : (j & 3)]);
+        for (int j = 0; j < 8; ++j) store_x(cx.xbuf, r0 + j, n, za[j] * ys[VAL ? 0 : (j & 3)]);
+        if (r0 + 16 < TR) {
+          MPDE_UNROLL
+          for (int j = 0; j < 8; ++j) za[j] = zl[(size_t)(r0 + 16 + j) * W];
+        }
+        MPDE_UNROLL
+        for (int j = 0; j < 8; ++j) store_x(cx.xbuf, r0 + 8 + j, n, zb2[j] * ys[VAL ? 0 : (j & 3)]);
       }
       fence_proxy_async_smem();
       tc_fence_before();

@@ -14,7 +14,7 @@ struct TcParams {
   const int* wshift;               // [T or 1][2*TC_MAX_L]   weight shift per step (hidden layers 1..L-1, output layer at L)
   long long wshift_stride;
   // GRAD / HVP (spills consumed by tc_wgrad_kernel; all indexed per task)
-  float* rec;                      // activation records: per (seg tile, layer): [NF][PTS][W]
+  float* rec;                      // activation records: per (seg tile, layer): [NF][W/128][PTS][128]
   long long rec_task_stride;       // floats
   long long rec_seg_base[MAX_SEG]; // floats, first tile of the segment inside the task's block
   float* zsp;                      // pre-activation adjoints zbar_l, l = 1..L-1: per (task tile, l-1): [TR rows][W]
