@@ -108,19 +108,26 @@ int tc_launch_prep(int W, int L, int OUT, int T, int with_bwd, const float* thet
 
 
 // ---- hidden-layer weight gradients from the spills (tc_wgrad.cuh) ----
+template <int W, bool HV> static cudaError_t wgrad_attr() {
+  return cudaFuncSetAttribute(tc_wgrad_kernel<W, HV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgGeo<W, HV>::SMEM);
+}
+template <int W, bool HV> static void wgrad_launch(const TcWgradParams* p, dim3 grid, void* stream) {
+  tc_wgrad_kernel<W, HV><<<grid, dim3(WgGeo<W, HV>::NT, 1, 1), WgGeo<W, HV>::SMEM, (cudaStream_t)stream>>>(*p);
+}
 int tc_launch_wgrad(const TcWgradParams* p, void* stream) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&]() {
-    attr_err = cudaFuncSetAttribute(tc_wgrad_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgGeo<128>::SMEM);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(tc_wgrad_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgGeo<256>::SMEM);
+    attr_err = wgrad_attr<128, false>();
+    if (attr_err == cudaSuccess) attr_err = wgrad_attr<128, true>();
+    if (attr_err == cudaSuccess) attr_err = wgrad_attr<256, false>();
+    if (attr_err == cudaSuccess) attr_err = wgrad_attr<256, true>();
   });
   if (attr_err != cudaSuccess) return 4;
   g_launches++;
   const dim3 grid((p->W / 128) * (p->L - 1), p->T, 1);
-  if (p->W == 128) tc_wgrad_kernel<128><<<grid, dim3(WgGeo<128>::NT, 1, 1), WgGeo<128>::SMEM, (cudaStream_t)stream>>>(*p);
-  else tc_wgrad_kernel<256><<<grid, dim3(WgGeo<256>::NT, 1, 1), WgGeo<256>::SMEM, (cudaStream_t)stream>>>(*p);
+  if (p->W == 128) { if (p->want_hv) wgrad_launch<128, true>(p, grid, stream); else wgrad_launch<128, false>(p, grid, stream); }
+  else { if (p->want_hv) wgrad_launch<256, true>(p, grid, stream); else wgrad_launch<256, false>(p, grid, stream); }
   return cudaGetLastError() != cudaSuccess ? 4 : 0;
 }
 

@@ -35,18 +35,22 @@ TC_DEV void split_tf32(float x, float& hi, float& lo) { hi = tf32_rn(x); lo = tf
 
 constexpr int WG_QR = 16;                    // rows per pipeline step
 constexpr int WG_GROUP = 8;                  // steps per accumulator generation (128 rows)
-constexpr int WG_NS = 3;                     // raw staging stages
 
-template <int W> struct WgGeo {
+// HV = true: H v products (tangent pairs need up to 9 record fields per point); false: gradients (5 fields).  The raw
+// ring takes what is left of the 227 KB after the two operand slots: 3 stages of 34 KB, or 5 stages of 26 KB (the
+// kernel is latency-bound on the spill reads: ncu r01f, 63 % of the raw_full waits miss with 3 stages).
+template <int W, bool HV> struct WgGeo {
   static constexpr int NMT = W / 128;
   static constexpr int HBYTES = 128 * 128, ZBYTES = W * 128;  // K-major slabs [128 k] / [W n] x (16 r hi | 16 r lo) tf32
   static constexpr int SLOT = HBYTES + ZBYTES;
   static constexpr int RAWZ = WG_QR * W * 4;                  // 16 rows of zbar, fp32
-  static constexpr int RAWH = 9 * 4 * 512;                    // <= 9 fields x 4 points (or 2 fields x 16 points) x 128 neurons
+  static constexpr int RAWH = (HV ? 9 : 5) * 4 * 512;         // fields x 4 points (or <= 2 fields x 16 points) x 128 neurons
   static constexpr int RAW = RAWZ + RAWH;
+  static constexpr int NS = HV ? 3 : 5;                       // raw staging stages
   static constexpr int NGRP = 2, NCONV = 256 * NGRP, NT = NCONV + 64;   // + MMA warp + producer warp
-  static constexpr int NBAR = 2 * WG_NS + 8;                  // raw full/empty, operand full/empty, dfull, dfree
-  static constexpr int SMEM = 2 * SLOT + WG_NS * RAW + NBAR * 8 + 16;
+  static constexpr int NBAR = 2 * NS + 8;                     // raw full/empty, operand full/empty, dfull, dfree
+  static constexpr int SMEM = 2 * SLOT + NS * RAW + NBAR * 8 + 16;
+  static_assert(SMEM <= 232448, "tc_wgrad_kernel: shared memory");
 };
 
 // 16-byte chunk `chunk` (4 consecutive rows; chunks 0..3 = hi, 4..7 = lo) of slab row `row`, swizzled
@@ -126,10 +130,11 @@ TC_DEV void wg_convert_h(const float* hraw, float om, uint8_t* hslab, int k, int
 
 // step st -> what it contracts
 struct WgStep { int s, jk, tile, t, qq; bool tan, zd; };
-TC_DEV WgStep wg_decode_step(const TcWgradParams& p, int st, int qpt, int npair) {
+// qpt (steps per tile: 4 or 8) and npair (1 or 2) are powers of two: shifts, no integer division in the step loop
+TC_DEV WgStep wg_decode_step(const TcWgradParams& p, int st, int qpt_log2, int npair_log2) {
   WgStep w;
-  const int pair = st % npair, q = st / npair;
-  w.t = q / qpt; w.qq = q % qpt;
+  const int pair = st & ((1 << npair_log2) - 1), q = st >> npair_log2;
+  w.t = q >> qpt_log2; w.qq = q & ((1 << qpt_log2) - 1);
   int s = 0;
   while (s + 1 < p.n_seg && w.t >= p.seg_tile_begin[s + 1]) ++s;
   w.s = s; w.jk = p.seg_jk[s]; w.tile = w.t - p.seg_tile_begin[s];
@@ -139,9 +144,10 @@ TC_DEV WgStep wg_decode_step(const TcWgradParams& p, int st, int qpt, int npair)
   return w;
 }
 
-template <int W>
-__global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_constant__ TcWgradParams p) {
-  typedef WgGeo<W> G;
+template <int W, bool HV>
+__global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __grid_constant__ TcWgradParams p) {
+  typedef WgGeo<W, HV> G;
+  constexpr int WG_NS = G::NS;
   uint8_t* smem = tc_smem_raw;
   uint8_t* raw = smem + 2 * G::SLOT;
   uint64_t* bars = reinterpret_cast<uint64_t*>(raw + WG_NS * G::RAW);
@@ -160,6 +166,7 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
   const int qpt = p.tile_rows / WG_QR;                 // 16-row steps per tile
   const int npair = p.want_hv ? 2 : 1;
   const int nsteps = n_tiles * qpt * npair;
+  const int qpt_log2 = 31 - __clz(qpt), npair_log2 = npair - 1;
   if (tid == 0) {
     if (smem_u32(smem) & 1023u) { printf("tc_wgrad_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     for (int i = 0; i < WG_NS; ++i) { mbar_init(&raw_full[i], 1); mbar_init(&raw_empty[i], 256); }
@@ -204,16 +211,16 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
     int done_gen = 0;                                   // generations 0 .. done_gen-1 are in the master copy
     const float om = p.omega;
     for (int st = grp; st < nsteps; st += G::NGRP) {
-      const WgStep w = wg_decode_step(p, st, qpt, npair);
+      const WgStep w = wg_decode_step(p, st, qpt_log2, npair_log2);
       // promotion lags the MMAs by two steps (no pipeline drain at a generation boundary)
       while (st >= 2 && done_gen < (st - 2) / WG_GROUP) promote(done_gen++);
-      const int stage = st % WG_NS;
+      const int stage = (int)((unsigned)st % (unsigned)WG_NS);
       const float* zraw = reinterpret_cast<const float*>(raw + (size_t)stage * G::RAW);
       const float* hraw = reinterpret_cast<const float*>(raw + (size_t)stage * G::RAW + G::RAWZ);
       mbar_wait(&raw_full[stage], (st / WG_NS) & 1);                      // the step's raw spills have landed
       if (st >= 2) mbar_wait(&op_empty[grp], ((st >> 1) - 1) & 1);        // the MMAs of step st - 2 have read the slot
       wg_convert_z<W>(zraw, zslab, gtid);
-      if (!w.tan) {
+      if (!HV || !w.tan) {
         if (w.jk == JET_V) wg_convert_h<JET_V, false>(hraw, om, hslab, k, half);
         else if (w.jk == JET_G) wg_convert_h<JET_G, false>(hraw, om, hslab, k, half);
         else if (w.jk == JET_LAP) wg_convert_h<JET_LAP, false>(hraw, om, hslab, k, half);
@@ -263,8 +270,8 @@ __global__ void __launch_bounds__(WgGeo<W>::NT, 1) tc_wgrad_kernel(const __grid_
     // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lanes 1..: one record field each) =====
     const float* rec_t = p.rec + (size_t)task * p.rec_task_stride;
     for (int st = 0; st < nsteps; ++st) {
-      const WgStep w = wg_decode_step(p, st, qpt, npair);
-      const int stage = st % WG_NS;
+      const WgStep w = wg_decode_step(p, st, qpt_log2, npair_log2);
+      const int stage = (int)((unsigned)st % (unsigned)WG_NS);
       const int CP = w.jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP, p0 = w.qq * npts;
       const int NF = w.jk == JET_V ? 2 : (w.jk == JET_G ? 4 : 5);
       const int NFT = NF + (p.hvp_records ? (w.jk == JET_V ? 1 : (w.jk == JET_G ? 3 : 4)) : 0);
