@@ -288,6 +288,15 @@ def run_ours(args, wl, name):
     fp32_peak, fp32_src = 71.6, "profiles/r01_microbench_pipes.jsonl (FFMA microbench on this pool's B200, 296 CTAs)"
     tensor_peak = peaks.get("bf16_tflops_sustained", 1400.0)
     tc = W in (128, 256) and os.environ.get("MPDE_DISABLE_TC", "0") != "1"
+    # dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed `ncu --set full` capture of the same
+    # kernel at this workload (profiles/ncu_traffic.json, written by tools/gpu_ncu_full.sh); null for other workloads
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if tj.get("workload") == name and world == 1:
+            traffic = tj["kernels"].get("tc_hvp_kernel" if tc else "pde_kernel_hvp", {}).get("traffic_bytes")
+    except (OSError, ValueError, KeyError):
+        pass
     share = {"hvp": hvp_ms / ms_total, "grad": grad_ms / ms_total, "loss": loss_ms / ms_total, "tc_wgrad": wgrad_ms / ms_total}
     per_mode = {"hvp": [hvp_ms, hvp_n], "grad": [grad_ms, grad_n], "loss": [loss_ms, loss_n], "tc_wgrad": [wgrad_ms, wgrad_n]}
     if tc:
@@ -305,7 +314,7 @@ def run_ours(args, wl, name):
             "frac_issued": (3.0 * achieved / tensor_peak) if achieved else None,
             "note": "achieved = ALGORITHMIC fp32 flops; each is 3 fp16 tensor-core flops (a_hi*b_hi + a_lo*b_hi + a_hi*b_lo), "
                     "so frac_issued = 3*frac is the tensor-pipe occupancy and 1/3 is the ceiling of frac at fp32 accuracy",
-            "traffic": None, "flops_per_launch": hvp_flops, "avg_launch_ms": hvp_ms / max(hvp_n, 1), "launches_timed": hvp_n,
+            "traffic": traffic, "flops_per_launch": hvp_flops, "avg_launch_ms": hvp_ms / max(hvp_n, 1), "launches_timed": hvp_n,
             "kernel_share_of_step": share, "per_mode_ms": per_mode,
         }
     else:
@@ -316,7 +325,7 @@ def run_ours(args, wl, name):
             "peak_source": "of measured: " + fp32_src,
             "tensor_peak_bf16_sustained": tensor_peak,
             "frac_of_tensor_peak": (achieved / tensor_peak) if achieved else None,
-            "traffic": None,
+            "traffic": traffic,
             "flops_per_launch": hvp_flops, "avg_launch_ms": hvp_ms / max(hvp_n, 1), "launches_timed": hvp_n,
             "kernel_share_of_step": share, "per_mode_ms": per_mode,
         }

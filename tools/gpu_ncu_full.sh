@@ -13,5 +13,9 @@ while [ $# -ge 2 ]; do
   ncu -i /tmp/${TAG}_$KN.ncu-rep --page raw --csv 2>/dev/null | gzip > $OUT/${TAG}_${KN}_raw.csv.gz
   ncu -i /tmp/${TAG}_$KN.ncu-rep --page source --csv 2>/dev/null | gzip > $OUT/${TAG}_${KN}_source.csv.gz
   ncu -i /tmp/${TAG}_$KN.ncu-rep --page details 2>/dev/null > $OUT/${TAG}_${KN}_details.txt
+  TRAFFIC_ARGS="${TRAFFIC_ARGS:-} $KN $OUT/${TAG}_${KN}_raw.csv.gz"
+  python tools/ncu_source_summary.py $OUT/${TAG}_${KN}_source.csv.gz 25 > $OUT/${TAG}_${KN}_source_summary.txt 2>&1
+  python tools/ncu_source_bins.py $OUT/${TAG}_${KN}_source.csv.gz 400 >> $OUT/${TAG}_${KN}_source_summary.txt 2>&1
 done
+python tools/ncu_traffic.py $TRAFFIC_ARGS > $OUT/${TAG}_traffic.json 2>&1
 ls -la $OUT | tail
