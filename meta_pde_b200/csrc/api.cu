@@ -125,6 +125,7 @@ struct EvalPlan {
   size_t n_wimg, n_wshift;  // floats: tc weight image [T][image], shifts [T][2*TC_MAX_L]
   size_t n_rec, n_zsp, n_psmall;          // tc GRAD spills (floats) and per-CTA small-parameter partials
   size_t n_wimg_d, n_wshift_d, n_zspd, n_psmall_h;   // tc HVP: direction image / shifts, zbardot spill, H v partials
+  size_t n_wpart; int wg_splits;                     // tc_wgrad row splits: partial results of splits 1..wg_splits-1
   long long rec_seg_base[MAX_SEG]; long long rec_per_task, zsp_per_task; int PS;
   size_t bytes;
 };
@@ -207,6 +208,7 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   pl->n_wimg = 0; pl->n_wshift = 0;
   pl->n_rec = pl->n_zsp = pl->n_psmall = 0; pl->PS = 0; pl->rec_per_task = pl->zsp_per_task = 0;
   pl->n_wimg_d = pl->n_wshift_d = pl->n_zspd = pl->n_psmall_h = 0;
+  pl->n_wpart = 0; pl->wg_splits = 1;
 #ifndef MPDE_EMU
   if (pl->tc) {
     pl->n_wimg = (size_t)T * (tc_image_bytes(pl->W, pl->L, mode != MODE_LOSS) / 4);
@@ -225,6 +227,18 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
       pl->zsp_per_task = (long long)tiles * (pl->L - 1) * (mode == MODE_HVP ? 64 : 128) * pl->W;
       pl->PS = tc::ps_count(pl->W, pl->L, pl->OUT);
       pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS;
+      {
+        // tc_wgrad_kernel: one CTA per (task, layer, k tile) and row split; splits chosen to fill whole waves of the
+        // SMs (512 items at T = 64: 3.46 waves -> 2 splits = 6.92; 64 items at T = 8: 0.43 -> 2 splits)
+        const long long items = (long long)T * (pl->L - 1) * (pl->W / 128), sms = device_sm_count();
+        int best = 1; double best_cost = 1e300;
+        for (int rs = 1; rs <= 8 && rs <= tiles; ++rs) {
+          const double cost = (double)((items * rs + sms - 1) / sms) / rs + 0.02 * rs;
+          if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = rs; }
+        }
+        pl->wg_splits = best;
+        pl->n_wpart = (size_t)(best - 1) * T * (pl->L - 1) * pl->W * pl->W;
+      }
       if (mode == MODE_HVP) {
         pl->n_wimg_d = pl->n_wimg; pl->n_wshift_d = pl->n_wshift; pl->n_zspd = pl->n_zsp; pl->n_psmall_h = pl->n_psmall;
       }
@@ -234,7 +248,7 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
   Carver c(nullptr, 0);
   c.take(pl->n_th); c.take(pl->n_thd); c.take(pl->n_scratch); c.take(pl->n_pg); c.take(pl->n_ph); c.take(pl->n_pt); c.take(pl->n_gtmp);
   c.take(pl->n_wimg); c.take(pl->n_wshift); c.take(pl->n_rec); c.take(pl->n_zsp); c.take(pl->n_psmall);
-  c.take(pl->n_wimg_d); c.take(pl->n_wshift_d); c.take(pl->n_zspd); c.take(pl->n_psmall_h);
+  c.take(pl->n_wimg_d); c.take(pl->n_wshift_d); c.take(pl->n_zspd); c.take(pl->n_psmall_h); c.take(pl->n_wpart);
   pl->bytes = c.off + 256;
   return MPDE_OK;
 }
@@ -276,8 +290,8 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
   float* wimg = c.take(pl.n_wimg); float* wshift = c.take(pl.n_wshift);
   float* rec = c.take(pl.n_rec); float* zsp = c.take(pl.n_zsp); float* psmall = c.take(pl.n_psmall);
   float* wimg_d = c.take(pl.n_wimg_d); float* wshift_d = c.take(pl.n_wshift_d); float* zspd = c.take(pl.n_zspd);
-  float* psmall_h = c.take(pl.n_psmall_h);
-  (void)wimg; (void)wshift; (void)rec; (void)zsp; (void)psmall; (void)wimg_d; (void)wshift_d; (void)zspd; (void)psmall_h;
+  float* psmall_h = c.take(pl.n_psmall_h); float* wpart = c.take(pl.n_wpart);
+  (void)wimg; (void)wshift; (void)rec; (void)zsp; (void)psmall; (void)wimg_d; (void)wshift_d; (void)zspd; (void)psmall_h; (void)wpart;
   if (mode != MODE_HVP) thd = nullptr;
 
   // 1. prep: theta -> theta-hat (shared theta: prepared once)
@@ -386,6 +400,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     }
     wp.rec = rec; wp.rec_task_stride = pl.rec_per_task; wp.zsp = zsp; wp.zsp_task_stride = pl.zsp_per_task;
     wp.gout = gout; wp.g_stride = pl.P;
+    wp.row_splits = pl.wg_splits; wp.part = wpart; wp.part_stride = (long long)T * (pl.L - 1) * pl.W * pl.W;
     if (mode == MODE_GRAD || want_grad) {
       cudaEvent_t ws; const bool wprof = prof_begin(3, stream, &ws);
       rc = tc_launch_wgrad(&wp, stream);

@@ -108,6 +108,16 @@ int tc_launch_prep(int W, int L, int OUT, int T, int with_bwd, const float* thet
 
 
 // ---- hidden-layer weight gradients from the spills (tc_wgrad.cuh) ----
+__global__ void __launch_bounds__(256) tc_wgrad_reduce_kernel(int W, int L, int rs, const float* part, long long part_stride,
+                                                              float* gout, long long g_stride) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x, l = 1 + blockIdx.y, t = blockIdx.z;
+  if (e >= W * W) return;
+  float* o = gout + (size_t)t * g_stride + nat_off_layer(W, l) + e;
+  float acc = *o;
+  for (int z = 1; z < rs; ++z) acc += part[(size_t)(z - 1) * part_stride + ((size_t)t * (L - 1) + (l - 1)) * W * W + e];
+  *o = acc;
+}
+
 template <int W, bool HV> static cudaError_t wgrad_attr() {
   return cudaFuncSetAttribute(tc_wgrad_kernel<W, HV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgGeo<W, HV>::SMEM);
 }
@@ -125,10 +135,18 @@ int tc_launch_wgrad(const TcWgradParams* p, void* stream) {
   });
   if (attr_err != cudaSuccess) return 4;
   g_launches++;
-  const dim3 grid((p->W / 128) * (p->L - 1), p->T, 1);
+  const int rs = p->row_splits > 1 ? p->row_splits : 1;
+  const dim3 grid((p->W / 128) * (p->L - 1), p->T, rs);
   if (p->W == 128) { if (p->want_hv) wgrad_launch<128, true>(p, grid, stream); else wgrad_launch<128, false>(p, grid, stream); }
   else { if (p->want_hv) wgrad_launch<256, true>(p, grid, stream); else wgrad_launch<256, false>(p, grid, stream); }
-  return cudaGetLastError() != cudaSuccess ? 4 : 0;
+  if (cudaGetLastError() != cudaSuccess) return 4;
+  if (rs > 1) {   // gout(hidden kernels) += parts of splits 1..rs-1, fixed order
+    g_launches++;
+    const dim3 rgrid((p->W * p->W + 255) / 256, p->L - 1, p->T);
+    tc_wgrad_reduce_kernel<<<rgrid, 256, 0, (cudaStream_t)stream>>>(p->W, p->L, rs, p->part, p->part_stride, p->gout, p->g_stride);
+    if (cudaGetLastError() != cudaSuccess) return 4;
+  }
+  return 0;
 }
 
 // ---- fixed-order sum of the per-CTA small-parameter partials into the natural gradient layout ----

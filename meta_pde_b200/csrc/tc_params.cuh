@@ -46,6 +46,8 @@ struct TcWgradParams {
   const float* zsp; long long zsp_task_stride;     // zbar_l
   const float* zspd;                               // zbardot_l (HVP spills), same layout and stride
   float* gout; long long g_stride;          // [T][P] natural layout; hidden kernels are written (not accumulated)
+  int row_splits;                           // grid.z: split z contracts tiles [n_tiles*z/splits, n_tiles*(z+1)/splits)
+  float* part; long long part_stride;       // results of splits 1.. : [split-1][T][L-1][W][W], summed into gout in fixed order
 };
 
 struct HvParams {

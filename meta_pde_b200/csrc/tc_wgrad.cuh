@@ -165,8 +165,11 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
   const int n_tiles = p.seg_tile_begin[p.n_seg];
   const int qpt = p.tile_rows / WG_QR;                 // 16-row steps per tile
   const int npair = p.want_hv ? 2 : 1;
-  const int nsteps = n_tiles * qpt * npair;
   const int qpt_log2 = 31 - __clz(qpt), npair_log2 = npair - 1;
+  // row split blockIdx.z: tiles [t_lo, t_hi) of the task; steps are counted from 0 inside the split
+  const int t_lo = (int)((long long)n_tiles * blockIdx.z / gridDim.z), t_hi = (int)((long long)n_tiles * (blockIdx.z + 1) / gridDim.z);
+  const int st0 = t_lo * qpt * npair;
+  const int nsteps = (t_hi - t_lo) * qpt * npair;
   if (tid == 0) {
     if (smem_u32(smem) & 1023u) { printf("tc_wgrad_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     for (int i = 0; i < WG_NS; ++i) { mbar_init(&raw_full[i], 1); mbar_init(&raw_empty[i], 256); }
@@ -211,7 +214,7 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
     int done_gen = 0;                                   // generations 0 .. done_gen-1 are in the master copy
     const float om = p.omega;
     for (int st = grp; st < nsteps; st += G::NGRP) {
-      const WgStep w = wg_decode_step(p, st, qpt_log2, npair_log2);
+      const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
       // promotion lags the MMAs by two steps (no pipeline drain at a generation boundary)
       while (st >= 2 && done_gen < (st - 2) / WG_GROUP) promote(done_gen++);
       const int stage = (int)((unsigned)st % (unsigned)WG_NS);
@@ -236,9 +239,11 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
       mbar_arrive(&op_full[grp]);
     }
     // ===== remaining generations, then the result: [128 k][W n] -> grad W_l =====
-    while (done_gen <= (nsteps - 1) / WG_GROUP) promote(done_gen++);
-    float* out = p.gout + (size_t)task * p.g_stride + nat_off_layer(W, l) + (size_t)(kt * 128 + 32 * (warp & 3) + lane) * W +
-                 (warp >> 2) * MC;
+    while (nsteps > 0 && done_gen <= (nsteps - 1) / WG_GROUP) promote(done_gen++);
+    float* out = (blockIdx.z == 0)
+                     ? p.gout + (size_t)task * p.g_stride + nat_off_layer(W, l)
+                     : p.part + (size_t)(blockIdx.z - 1) * p.part_stride + ((size_t)task * (L - 1) + (l - 1)) * W * W;
+    out += (size_t)(kt * 128 + 32 * (warp & 3) + lane) * W + (warp >> 2) * MC;
     MPDE_UNROLL
     for (int j = 0; j < MC; ++j) out[j] = master[j];   // gout rows are only 4-byte aligned (P is odd-ish)
   } else if (warp == G::NCONV / 32) {
@@ -270,7 +275,7 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
     // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lanes 1..: one record field each) =====
     const float* rec_t = p.rec + (size_t)task * p.rec_task_stride;
     for (int st = 0; st < nsteps; ++st) {
-      const WgStep w = wg_decode_step(p, st, qpt_log2, npair_log2);
+      const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
       const int stage = (int)((unsigned)st % (unsigned)WG_NS);
       const int CP = w.jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP, p0 = w.qq * npts;
       const int NF = w.jk == JET_V ? 2 : (w.jk == JET_G ? 4 : 5);

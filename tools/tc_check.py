@@ -28,7 +28,8 @@ def parity():
 def timing(modes=("loss",)):
     K = ops.kernels(torch.device("cuda:0"))
     dev = K.device
-    for (W, L, T, n) in [(256, 5, 64, 16384), (128, 5, 64, 16384)]:
+    TT = int(os.environ.get("MPDE_T", "64"))
+    for (W, L, T, n) in [(256, 5, TT, 16384), (128, 5, TT, 16384)]:
         theta = synthetic.siren_theta([W] * L, 1, 30.0, 30.0, True, seed=0).to(dev)
         theta = theta.unsqueeze(0).repeat(T, 1).contiguous()
         sets, prm = synthetic.make_tasks("poisson", T, [n, n], seed=1)
