@@ -198,6 +198,10 @@ def run_ours(args, wl, name):
         raise SystemExit("bench.py: no CUDA device; this package has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # stdout carries exactly one JSON line: library chatter (e.g. NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     from meta_pde_b200 import synthetic, train
@@ -347,6 +351,8 @@ def run_ours(args, wl, name):
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(wl)
+    sys.stdout.flush()
+    os.dup2(stdout_fd, 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
