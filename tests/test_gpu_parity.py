@@ -39,6 +39,18 @@ def test_single_point_sets(gpu_kernels):
     pc.check_loss_grad_hvp(gpu_kernels, "poisson", 64, 2, 1, T=1, set_sizes=[1, 1])
 
 
+def test_tensor_core_path_edge_cases(gpu_kernels):
+    # widths 128 / 256 run the tcgen05 kernels + tc_wgrad_kernel
+    # one task, many tiles: tc_wgrad_kernel takes 8 row splits (grid.z) and the fixed-order reduce of the partial results
+    pc.check_loss_grad_hvp(gpu_kernels, "poisson", 128, 3, 1500, T=1)
+    # a ragged last tile in both sets, shared theta over 5 tasks, heavy boundary weight
+    pc.check_loss_grad_hvp(gpu_kernels, "poisson", 256, 2, 77, T=5, bc_weight=100.0, per_task_theta=False)
+    # one point per set: every tile is padding except one row
+    pc.check_loss_grad_hvp(gpu_kernels, "poisson", 128, 2, 1, T=1, set_sizes=[1, 1])
+    # three-channel jets (padded to four rows) and the value-only boundary sets of hyperelasticity, deeper net
+    pc.check_loss_grad_hvp(gpu_kernels, "hyper_elasticity", 256, 3, 90, T=2)
+
+
 def test_field_eval(gpu_kernels):
     pc.check_field_eval(gpu_kernels, 64, 3, 1, 1024, T=3)
     pc.check_field_eval(gpu_kernels, 64, 3, 2, 1000, T=2)
