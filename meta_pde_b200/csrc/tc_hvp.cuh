@@ -61,16 +61,57 @@ struct HvTile {
   static constexpr int CP = VAL ? 1 : 4;
   static constexpr int PTS = HR / CP;
 
+  // MN-major B operands (see TcTile in tc_kernels.cuh): one block of 64 rows, [k = neuron][128 B = 64 rows]; 8 consecutive
+  // rows of a neuron are one 16-byte chunk, so a point's 4 channels (or 8 rows) are stored with one vector store
+  static constexpr uint32_t LO_OFF = (uint32_t)W * 128u;                 // lo parts behind the hi parts
   static TC_DEV uint32_t xoff(int r, int n) {
-    return (uint32_t)(n >> 6) * G::SLAB + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u +
-           ((((uint32_t)(n & 63) >> 3) ^ (uint32_t)(r & 7)) << 4) + (uint32_t)(n & 7) * 2u;
+    return (uint32_t)(n >> 3) * 1024u + (uint32_t)(n & 7) * 128u + ((((uint32_t)r >> 3) ^ (uint32_t)(n & 7)) << 4) +
+           (uint32_t)(r & 7) * 2u;
   }
   static TC_DEV void store_x(uint8_t* xb, int r, int n, float y) {
     __half h, l;
     split_f16(y, h, l);
     const uint32_t o = xoff(r, n);
     *reinterpret_cast<__half*>(xb + o) = h;
-    *reinterpret_cast<__half*>(xb + G::KSL * G::SLAB + o) = l;
+    *reinterpret_cast<__half*>(xb + LO_OFF + o) = l;
+  }
+  static TC_DEV void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 f = __half22float2(h);
+    const __half2 l = __floats2half2_rn(a - f.x, b - f.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+  }
+  static TC_DEV void store_x4(uint8_t* xb, int r0, int n, const float (&y)[4]) {
+    uint2 hv, lv;
+    split2(y[0], y[1], hv.x, lv.x);
+    split2(y[2], y[3], hv.y, lv.y);
+    const uint32_t o = xoff(r0, n);
+    *reinterpret_cast<uint2*>(xb + o) = hv;
+    *reinterpret_cast<uint2*>(xb + LO_OFF + o) = lv;
+  }
+  static TC_DEV void store_x8(uint8_t* xb, int r0, int n, const float (&y)[8]) {
+    uint4 hv, lv;
+    split2(y[0], y[1], hv.x, lv.x);
+    split2(y[2], y[3], hv.y, lv.y);
+    split2(y[4], y[5], hv.z, lv.z);
+    split2(y[6], y[7], hv.w, lv.w);
+    const uint32_t o = xoff(r0, n);
+    *reinterpret_cast<uint4*>(xb + o) = hv;
+    *reinterpret_cast<uint4*>(xb + LO_OFF + o) = lv;
+  }
+  // one point: CP rows of the primal and of the tangent operand
+  static TC_DEV void store_point(uint8_t* xb, uint8_t* xdb, int pl, int n, const float* a, const float* ad, const float (&ys)[8]) {
+    if (VAL) {
+      store_x(xb, pl, n, a[0] * ys[0]);
+      store_x(xdb, pl, n, ad[0] * ys[4]);
+    } else {
+      float y4[4], yd4[4];
+      MPDE_UNROLL
+      for (int c = 0; c < 4; ++c) { y4[c] = c < C ? a[c] * ys[c] : 0.f; yd4[c] = c < C ? ad[c] * ys[4 + c] : 0.f; }
+      store_x4(xb, 4 * pl, n, y4);
+      store_x4(xdb, 4 * pl, n, yd4);
+    }
   }
   // bounds of |a_c| and |adot_c| from the pre-activation jets (no sincos)
   static TC_DEV void bound_update(float om, const float* z, const float* zd, float (&bnd)[8]) {
@@ -164,11 +205,7 @@ struct HvTile {
         for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
         MPDE_UNROLL
         for (int c = 0; c < C; ++c) recp[(size_t)((NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
-        MPDE_UNROLL
-        for (int c = 0; c < CP; ++c) {
-          store_x(cx.xbuf, CP * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
-          store_x(cx.xdbuf, CP * pl + c, n, c < C ? ad[c] * ys[4 + c] : 0.f);
-        }
+        store_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, ys);
       }
     }
     fence_proxy_async_smem();
@@ -228,11 +265,7 @@ struct HvTile {
           for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f)) * (PTS * W) + (pl) * 128] = sv[f];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
-          MPDE_UNROLL
-          for (int c = 0; c < CP; ++c) {
-            store_x(cx.xbuf, CP * pl + c, n, c < C ? a[c] * ys[c] : 0.f);
-            store_x(cx.xdbuf, CP * pl + c, n, c < C ? ad[c] * ys[4 + c] : 0.f);
-          }
+          store_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, ys);
         }
       }
       fence_proxy_async_smem();
@@ -445,9 +478,10 @@ struct HvTile {
         MPDE_UNROLL
         for (int j = 0; j < 8; ++j) {
           const int c = VAL ? 0 : (j & 3);
-          store_x(cx.xbuf, r0 + j, n, zv[j] * ys[c]);
-          store_x(cx.xdbuf, r0 + j, n, zdv[j] * ys[4 + c]);
+          zv[j] *= ys[c]; zdv[j] *= ys[4 + c];
         }
+        store_x8(cx.xbuf, r0, n, zv);
+        store_x8(cx.xdbuf, r0, n, zdv);
         if (r0 + 16 < HR) {
           MPDE_UNROLL
           for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)(r0 + 16 + j) * W]; zdv[j] = zld[(size_t)(r0 + 16 + j) * W]; }
@@ -455,9 +489,10 @@ struct HvTile {
         MPDE_UNROLL
         for (int j = 0; j < 8; ++j) {
           const int c = VAL ? 0 : (j & 3);
-          store_x(cx.xbuf, r0 + 8 + j, n, zv2[j] * ys[c]);
-          store_x(cx.xdbuf, r0 + 8 + j, n, zdv2[j] * ys[4 + c]);
+          zv2[j] *= ys[c]; zdv2[j] *= ys[4 + c];
         }
+        store_x8(cx.xbuf, r0 + 8, n, zv2);
+        store_x8(cx.xdbuf, r0 + 8, n, zdv2);
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -552,7 +587,8 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
   } else {
     // ===== MMA issuer =====
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 0);
+      constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
+      constexpr uint32_t LO_OFF = (uint32_t)W * 128u;
       const uint32_t xb = smem_u32(cx.xbuf), xdb = smem_u32(cx.xdbuf);
       uint32_t stage = 0, phase = 0, xpar = 0;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -569,14 +605,14 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
                 mbar_wait(&cx.full[stage], phase);
                 tc_fence_after();
                 const uint32_t a_hi = smem_u32(cx.ring + (size_t)stage * STAGE_BYTES), a_lo = a_hi + 16384u;
-                const uint32_t b_hi = xb + (uint32_t)s * G::SLAB, b_lo = b_hi + (uint32_t)G::KSL * G::SLAB;
-                const uint32_t c_hi = xdb + (uint32_t)s * G::SLAB, c_lo = c_hi + (uint32_t)G::KSL * G::SLAB;
+                const uint32_t b_hi = xb + (uint32_t)s * 8192u, b_lo = b_hi + LO_OFF;      // k0 = 64 s: 8 atoms of 8 neurons
+                const uint32_t c_hi = xdb + (uint32_t)s * 8192u, c_lo = c_hi + LO_OFF;
                 MPDE_UNROLL
                 for (int kk = 0; kk < 4; ++kk) {
                   const uint64_t ah = desc_kmajor(a_hi + kk * 32), al = desc_kmajor(a_lo + kk * 32);
-                  const uint64_t bh = desc_kmajor(b_hi + kk * 32), bl = desc_kmajor(b_lo + kk * 32);
+                  const uint64_t bh = desc_mnmajor(b_hi + kk * 2048, LO_OFF), bl = desc_mnmajor(b_lo + kk * 2048, LO_OFF);
                   if (which == 0) {
-                    const uint64_t ch = desc_kmajor(c_hi + kk * 32), cl = desc_kmajor(c_lo + kk * 32);
+                    const uint64_t ch = desc_mnmajor(c_hi + kk * 2048, LO_OFF), cl = desc_mnmajor(c_lo + kk * 2048, LO_OFF);
                     mma_f16_ss(d0, ah, bh, idesc, acc); mma_f16_ss(d0, al, bh, idesc, 1); mma_f16_ss(d0, ah, bl, idesc, 1);   // W * primal
                     mma_f16_ss(d1, ah, ch, idesc, acc); mma_f16_ss(d1, al, ch, idesc, 1); mma_f16_ss(d1, ah, cl, idesc, 1);   // W * tangent
                   } else {
