@@ -26,7 +26,9 @@ template <int W> struct HvGeo {
   static constexpr int MISC = 2 * HR * 4 + 2 * HR * 4 + 2 * HR * 4 + HR * 4 + 64 + 16 + (2 * NSTAGE + 3) * 8 + 16;
   static constexpr int SMEM = 2 * XBYTES + RING + MISC;
   static constexpr int TMEM_COLS = 512;                 // 3 accumulator sets x NMT x 64 columns (<= 384)
-  static constexpr int D0 = 0, D1 = NMT * HR, D2 = 2 * NMT * HR;   // primal, W*tangent, Wdot*primal
+  // TMEM columns: per M tile mt the pair [W*primal (64) | W*tangent (64)] at mt * 128 -- one N = 128 MMA over the two
+  // row blocks X | Xd, which share the A operand -- then Wdot*primal at D2 + mt * 64
+  static constexpr int D2 = 2 * NMT * HR;
 };
 
 template <int W> struct HvCtx {
@@ -167,7 +169,8 @@ struct HvTile {
     const float* prm = kp.prm + (size_t)task * kp.nprm;
     const int pt0 = tile * PTS;
     const float* pts = sg.pts + (size_t)task * sg.task_stride;
-    const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * HR);
+    const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), 0u);
+    const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR, c2 = (uint32_t)G::D2 + (uint32_t)mt * HR;   // accumulator columns
     float* xs = cx.xs;
     float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W +
              (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
@@ -227,7 +230,7 @@ struct HvTile {
       MPDE_NOUNROLL
       for (int ch = 0; ch < HR / 16; ++ch) {
         uint32_t v0[16], v1[16], v2[16];
-        tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+        tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
         tmem_ld_wait();
         MPDE_UNROLL
         for (int q = 0; q < PPC; ++q) {
@@ -247,7 +250,7 @@ struct HvTile {
       MPDE_NOUNROLL
       for (int ch = 0; ch < HR / 16; ++ch) {
         uint32_t v0[16], v1[16], v2[16];
-        tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+        tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
         tmem_ld_wait();
         MPDE_UNROLL
         for (int q = 0; q < PPC; ++q) {
@@ -286,7 +289,7 @@ struct HvTile {
         MPDE_NOUNROLL
         for (int ch = 0; ch < HR / 16; ++ch) {
           uint32_t v0[16], v1[16], v2[16];
-          tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+          tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
           tmem_ld_wait();
           if (lane < OUT) {
             MPDE_UNROLL
@@ -385,7 +388,7 @@ struct HvTile {
           MPDE_UNROLL
           for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + (ch * PPC + q) * 128];
         if (l < L - 1) {
-          tmem_ld16(tl + G::D0 + ch * 16, v0); tmem_ld16(tl + G::D1 + ch * 16, v1); tmem_ld16(tl + G::D2 + ch * 16, v2);
+          tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
           tmem_ld_wait();
         }
         MPDE_UNROLL
@@ -588,8 +591,9 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
+      constexpr uint32_t idesc2 = make_idesc(FMT_F16, 128, 2 * HR, 0, 1);  // N = 128: rows of X then rows of Xd
       constexpr uint32_t LO_OFF = (uint32_t)W * 128u;
-      const uint32_t xb = smem_u32(cx.xbuf), xdb = smem_u32(cx.xdbuf);
+      const uint32_t xb = smem_u32(cx.xbuf);              // Xd sits XBYTES behind X
       uint32_t stage = 0, phase = 0, xpar = 0;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         for (int step = 1; step <= nsteps; ++step) {
@@ -597,8 +601,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
           tc_fence_after();
           const int nmt = (step != L) ? G::NMT : 1;
           for (int mt = 0; mt < nmt; ++mt) {
-            const uint32_t d0 = tbase + G::D0 + (uint32_t)mt * HR, d1 = tbase + G::D1 + (uint32_t)mt * HR,
-                           d2 = tbase + G::D2 + (uint32_t)mt * HR;
+            const uint32_t d01 = tbase + (uint32_t)mt * 2u * HR, d2 = tbase + G::D2 + (uint32_t)mt * HR;
             for (int which = 0; which < 2; ++which) {
               uint32_t acc = 0;
               for (int s = 0; s < G::KSL; ++s) {
@@ -606,15 +609,15 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
                 tc_fence_after();
                 const uint32_t a_hi = smem_u32(cx.ring + (size_t)stage * STAGE_BYTES), a_lo = a_hi + 16384u;
                 const uint32_t b_hi = xb + (uint32_t)s * 8192u, b_lo = b_hi + LO_OFF;      // k0 = 64 s: 8 atoms of 8 neurons
-                const uint32_t c_hi = xdb + (uint32_t)s * 8192u, c_lo = c_hi + LO_OFF;
                 MPDE_UNROLL
                 for (int kk = 0; kk < 4; ++kk) {
                   const uint64_t ah = desc_kmajor(a_hi + kk * 32), al = desc_kmajor(a_lo + kk * 32);
                   const uint64_t bh = desc_mnmajor(b_hi + kk * 2048, LO_OFF), bl = desc_mnmajor(b_lo + kk * 2048, LO_OFF);
                   if (which == 0) {
-                    const uint64_t ch = desc_mnmajor(c_hi + kk * 2048, LO_OFF), cl = desc_mnmajor(c_lo + kk * 2048, LO_OFF);
-                    mma_f16_ss(d0, ah, bh, idesc, acc); mma_f16_ss(d0, al, bh, idesc, 1); mma_f16_ss(d0, ah, bl, idesc, 1);   // W * primal
-                    mma_f16_ss(d1, ah, ch, idesc, acc); mma_f16_ss(d1, al, ch, idesc, 1); mma_f16_ss(d1, ah, cl, idesc, 1);   // W * tangent
+                    // W * [primal | tangent]: the second block of 64 rows is Xd, XBYTES behind X (leading byte offset)
+                    const uint64_t bh2 = desc_mnmajor(b_hi + kk * 2048, (uint32_t)G::XBYTES);
+                    const uint64_t bl2 = desc_mnmajor(b_lo + kk * 2048, (uint32_t)G::XBYTES);
+                    mma_f16_ss(d01, ah, bh2, idesc2, acc); mma_f16_ss(d01, al, bh2, idesc2, 1); mma_f16_ss(d01, ah, bl2, idesc2, 1);
                   } else {
                     mma_f16_ss(d2, ah, bh, idesc, acc); mma_f16_ss(d2, al, bh, idesc, 1); mma_f16_ss(d2, ah, bl, idesc, 1);   // Wdot * primal
                   }

@@ -347,7 +347,6 @@ struct TcTile {
         tmem_ld32(tlane + ch * 32, v);
         tmem_ld_wait();
         if (VAL) {
-          MPDE_UNROLL
           float y8[8];
           MPDE_UNROLL
           for (int q = 0; q < 32; ++q) {
