@@ -150,6 +150,12 @@ class Kernels:
 
     def workspace(self, nbytes):
         if self._ws is None or self._ws.numel() < nbytes:
+            # release the old buffer first: at C5 size the tensor-core path's spills take 60-115 GB, and old + new
+            # would not fit in the 180 GB (the stream is synchronised so that no launch still uses the old one)
+            if self._ws is not None and self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+                self._ws = None
+                torch.cuda.empty_cache()
             self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
         return self._ws
 

@@ -134,3 +134,31 @@ def test_c5_directional_derivative(c5):
     fd = (lp[0].double() - lm[0].double()) / (2 * eps)
     an = float((grad[0].double() * d.double()).sum())
     assert abs(float(fd) - an) <= 2e-2 * abs(an), (float(fd), an)
+
+
+@pytest.mark.parametrize("pde,W,L,out", [("td_burgers", 256, 5, 1), ("hyper_elasticity", 256, 5, 2), ("td_burgers", 128, 8, 1)])
+def test_full_size_properties_other_pdes(gpu_kernels, pde, W, L, out):
+    """16384-point sets of the other two PDEs on the tensor-core path (ragged 63-point boundary sets for Burgers,
+    three-channel jets and value-only boundary sets for hyperelasticity): finite outputs, the gradient of the H v call
+    equals the GRAD call, H v is linear and symmetric in v.  tools/scale_check.py runs the same at 64 tasks."""
+    K = gpu_kernels
+    T, n = 2, 16384
+    theta = synthetic.siren_theta([W] * L, out, 30.0, 30.0, True, seed=0).to(K.device).unsqueeze(0).repeat(T, 1).contiguous()
+    sets, prm = synthetic.make_tasks(pde, T, synthetic.default_set_sizes(pde, n), seed=1)
+    sets = [s.to(K.device) for s in sets]
+    prm = prm.to(K.device)
+    net = K.net_desc(L, W, out, 30.0, True)
+    g = torch.Generator().manual_seed(3)
+    v1 = torch.randn(theta.shape, generator=g).to(K.device)
+    v2 = torch.randn(theta.shape, generator=g).to(K.device)
+    l0, _, g0 = K.loss_grad(net, pde, 1.0, theta, sets, prm, T)
+    l1, _, g1, h1 = K.loss_hvp(net, pde, 1.0, theta, v1, sets, prm, T)
+    _, _, _, h2 = K.loss_hvp(net, pde, 1.0, theta, v2, sets, prm, T)
+    _, _, _, h12 = K.loss_hvp(net, pde, 1.0, theta, (v1 + 0.5 * v2).contiguous(), sets, prm, T)
+    torch.cuda.synchronize()
+    rel = lambda a, b: float((a - b).norm() / b.norm())
+    assert torch.isfinite(g0).all() and torch.isfinite(h1).all()
+    assert rel(l1, l0) < 1e-5 and rel(g1, g0) < 1e-4          # tolerance: north_star rel 1e-4
+    assert rel(h12, h1 + 0.5 * h2) < 1e-4
+    s12, s21 = (h1 * v2).sum(1), (h2 * v1).sum(1)
+    assert float((s12 - s21).abs().max() / s12.abs().max()) < 1e-3
