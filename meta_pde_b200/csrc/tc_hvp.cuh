@@ -4,10 +4,11 @@
 // Same machinery as tc_pde_kernel (tc_kernels.cuh) with a tangent stream next to the primal one:
 //   forward   z    = W^T h,      zdot    = W^T hdot    + Wdot^T h
 //   reverse   abar = W zbar,     abardot = W zbardot   + Wdot zbar
-// A tile is 64 jet rows (16 points x 4 channels, or 64 value points): two B operands X (h / zbar) and Xd
-// (hdot / zbardot) of 64 KB each stay in shared memory, three accumulator sets live in TMEM (primal, W * tangent,
-// Wdot * primal: the two tangent products carry different block shifts and are added in the epilogue), and the
-// weight ring streams, per M tile, the stages of W followed by the stages of Wdot (the direction's image).
+// A tile is 64 jet rows (16 points x 4 channels, or 64 value points): the primal rows X (h / zbar) and the tangent rows
+// Xd (hdot / zbardot) are two 64-row blocks of one MN-major B operand (64 KB each in shared memory), so W * [X | Xd] is
+// a single N = 128 MMA that reads the weight stage once, and Wdot * X an N = 64 one.  Three accumulator sets live in
+// TMEM (W * primal, W * tangent, Wdot * primal: the two tangent products carry different block shifts and are added in
+// the epilogue), and the weight ring streams, per M tile, the stages of W followed by the stages of Wdot.
 // Spills for tc_wgrad_kernel: records (saved fields + zdot) of every layer, zbar_l and zbardot_l.
 #pragma once
 #include "tc_kernels.cuh"

@@ -10,7 +10,7 @@
 //
 // Orientation ("transposed"): D[neuron][row] = sum_k Wt[neuron][k] * X[row][k].  The weights are the A operand
 // (M = 128 neurons per MMA, streamed from L2 through a bulk-copy ring, pre-swizzled by tc_prep_kernel), the tile's
-// jet rows are the B operand (N = 128 rows resident in shared memory), and a TMEM lane is a neuron: the epilogue
+// jet rows are the MN-major B operand (N = 128 rows resident in shared memory), and a TMEM lane is a neuron: the epilogue
 // thread of neuron n reads its accumulator row with tcgen05.ld and has all jet channels of every point of the tile
 // in registers, so the sin-jet algebra is thread-local exactly as in the FP32-FMA kernel.
 //
