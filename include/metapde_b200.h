@@ -85,7 +85,12 @@ int mpde_num_point_sets(int pde_kind);
 int mpde_num_terms(int pde_kind);
 int mpde_num_pde_params(int pde_kind);
 const char* mpde_status_string(int status);
-/* workspace for mpde_loss / mpde_loss_grad / mpde_loss_hvp (mode = mpde_mode) */
+/* workspace for mpde_loss / mpde_loss_grad / mpde_loss_hvp (mode = mpde_mode).
+ * Widths 32/64 (FP32-FMA kernels): per-CTA scratch and partial gradients, O(CTAs * P).
+ * Widths 128/256 (tensor-core kernels): additionally the activation records and the zbar (zbardot) spills of every
+ * point of every task, read once by the weight-gradient contraction: about 0.93 GB per task in GRAD mode and 1.8 GB per
+ * task in HVP mode at 5x256 with 16384 + 16384 points (60 / 115 GB at 64 tasks: sized for the 180 GB of a B200; shard
+ * the tasks over more GPUs or call with fewer tasks per launch when that does not fit). */
 size_t mpde_workspace_bytes(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, int mode);
 
 /* ---- K1: loss only.  Replaces pde.loss_fn + the driver wrapper
