@@ -1,4 +1,5 @@
-"""One call of a single mode at C5 size (for ncu captures): python tools/ncu_one.py grad|hvp|loss [reps]"""
+"""One call of a single mode at C5 size (for ncu captures): python tools/ncu_one.py grad|hvp|loss [reps]
+(MPDE_W / MPDE_L / MPDE_T / MPDE_N override the 5x256, 64 tasks, 16384 points)"""
 import os
 import sys
 
@@ -12,7 +13,8 @@ mode = sys.argv[1] if len(sys.argv) > 1 else "grad"
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 K = ops.kernels(torch.device("cuda:0"))
 dev = K.device
-W, L, T, n = 256, 5, 64, 16384
+W, L = int(os.environ.get("MPDE_W", "256")), int(os.environ.get("MPDE_L", "5"))
+T, n = int(os.environ.get("MPDE_T", "64")), int(os.environ.get("MPDE_N", "16384"))
 theta = synthetic.siren_theta([W] * L, 1, 30.0, 30.0, True, seed=0).to(dev).unsqueeze(0).repeat(T, 1).contiguous()
 sets, prm = synthetic.make_tasks("poisson", T, [n, n], seed=1)
 sets = [s.to(dev) for s in sets]
