@@ -180,7 +180,7 @@ def run_reference(args, wl, name):
 def bench_config(wl, name, n_gpus):
     return {"workload": name, "pde": wl["pde"], "siren": f"{wl['L']}x{wl['W']} omega=30", "meta_batch_tasks": wl["T"],
             "tasks_per_gpu": wl["T"] // n_gpus, "points_per_set": wl["n"], "inner_steps": wl["K"],
-            "second_order": True, "parallelism": f"task-sharded dp{n_gpus}",
+            "second_order": True, "parallelism": f"task-sharded dp{n_gpus}", "cuda_graph": bool(getattr(bench_config, "graph", False)),
             "l2_policy": "inputs larger than L2 (fresh point sets every step; per-step working set >> 126 MB)"}
 
 
@@ -215,7 +215,7 @@ def run_ours(args, wl, name):
     tr = train.MamlTrainer(pde, L, W, theta0, bsize=T, inner_steps=K, inner_lr=HYPER["inner_lr"], outer_lr=HYPER["outer_lr"],
                            lr_inner_lr=HYPER["lr_inner_lr"], siren_omega=HYPER["omega"], bc_weight=HYPER["bc_weight"],
                            inner_grad_clip=HYPER["inner_grad_clip"], grad_clip=HYPER["grad_clip"],
-                           outer_loss_decay=HYPER["outer_loss_decay"], device=dev)
+                           outer_loss_decay=HYPER["outer_loss_decay"], device=dev, use_cuda_graph=args.graph)
     Kn = tr.K
     sizes = synthetic.default_set_sizes(pde, n)
 
@@ -258,11 +258,11 @@ def run_ours(args, wl, name):
     # ---- warm-up, then EXACTLY `steps` timed steps with the points resident in HBM --------------------------
     for i in range(args.warmup):
         dev_step(i)
-    Kn.prof_enable(True)
+    Kn.prof_enable(not args.graph)          # event pairs cannot be recorded into a replayed graph
     launches0 = Kn.launch_count()
     with ClockSampler(local) as clk:
         ms_total = timed(dev_step, args.steps)
-    launches = Kn.launch_count() - launches0
+    launches = Kn.launch_count() - launches0 + (tr.graph_launches * args.steps if args.graph else 0)
     prof = {m: Kn.prof_read(m) for m in (MODE_LOSS, MODE_GRAD, MODE_HVP)}
     wgrad_ms, wgrad_n = Kn.prof_read(3)
     Kn.prof_enable(False)
@@ -366,8 +366,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graph", action="store_true",
+                    help="replay the rollout as one CUDA graph (launch-bound small configs; per-kernel timing is then off)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    bench_config.graph = args.graph
     if args.impl == "reference":
         run_reference(args, wl, args.workload)
     else:

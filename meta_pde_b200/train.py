@@ -93,7 +93,7 @@ class MamlTrainer:
 
     def __init__(self, pde, num_layers, layer_size, theta0, *, bsize, inner_steps, inner_lr, outer_lr, lr_inner_lr,
                  siren_omega=30.0, log_scale=True, bc_weight=1.0, inner_grad_clip=1e14, grad_clip=1e14,
-                 outer_loss_decay=0.1, optimizer="adam", device=None, group=None):
+                 outer_loss_decay=0.1, optimizer="adam", device=None, group=None, use_cuda_graph=False):
         self.K = ops.kernels(device)          # raises without CUDA / without the built library
         self.device = self.K.device
         self.pde = pde
@@ -123,6 +123,16 @@ class MamlTrainer:
         self.T_local = self.bsize // self.world
         self._packed = torch.empty((self.inner_steps + 1) * self.P, dtype=torch.float32, device=dev)
         self._dev_batch = None
+        # CUDA graph of the rollout (mpde_maml_outer: ~400 launches per step, which is what a step of the small
+        # published configs -- 3x64, 1024 points -- costs).  Captured on the first step for the batch
+        # shape seen there and replayed afterwards; the all-reduce and the optimizer updates (whose bias corrections
+        # are host scalars that change every step) stay outside the graph.
+        self.use_cuda_graph = bool(use_cuda_graph) and self.device.type == "cuda"
+        self._graph = None
+        self._graph_batch = None
+        self._graph_out = None
+        self._graph_key = None
+        self.graph_launches = 0
 
     # -- pieces (bench.py times them separately) ------------------------------------------------------------
     def stage(self, host_batch):
@@ -130,14 +140,40 @@ class MamlTrainer:
         self._dev_batch = host_batch.to(self.device, out=self._dev_batch)
         return self._dev_batch
 
+    def _rollout(self, batch):
+        inner, outer, final, aux = batch.views()
+        P, K = self.P, self.inner_steps
+        return self.K.maml_outer(self.net, self.pde, self.bc_weight, self.cfg, self.theta, self.inner_lrs, inner, outer,
+                                 final, aux, batch.pde_params, batch.T, grad_scale=1.0 / self.bsize,
+                                 out_g_theta=self._packed[:P], out_g_lrs=self._packed[P:].view(K, P))
+
+    def _rollout_graphed(self, batch):
+        key = (batch.T, tuple(batch.n_inner), tuple(batch.n_outer))
+        if self._graph is None or self._graph_key != key:
+            # static input buffers; one eager call first (workspace allocation, one-time function attributes), then
+            # capture on a side stream as torch.cuda.graph requires
+            self._graph_batch = MamlBatch(batch.pde, batch.T, batch.K, batch.n_inner, batch.n_outer,
+                                          torch.empty_like(batch.flat), torch.empty_like(batch.pde_params))
+            self._graph_batch.flat.copy_(batch.flat)
+            self._graph_batch.pde_params.copy_(batch.pde_params)
+            self._rollout(self._graph_batch)
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            n0 = self.K.launch_count()
+            with torch.cuda.graph(g):
+                self._graph_out = self._rollout(self._graph_batch)
+            self.graph_launches = self.K.launch_count() - n0     # kernel nodes replayed per step
+            self._graph, self._graph_key = g, key
+        if batch is not self._graph_batch:
+            self._graph_batch.flat.copy_(batch.flat, non_blocking=True)
+            self._graph_batch.pde_params.copy_(batch.pde_params, non_blocking=True)
+        self._graph.replay()
+        return self._graph_out
+
     def meta_grad(self, batch):
         """multi_task_grad_and_losses (maml.py:210-233) over the local tasks; returns the ABI result dict with
         g_theta / g_lrs holding (1/bsize) * SUM over local tasks (all-reduced when distributed)."""
-        inner, outer, final, aux = batch.views()
-        P, K = self.P, self.inner_steps
-        out = self.K.maml_outer(self.net, self.pde, self.bc_weight, self.cfg, self.theta, self.inner_lrs, inner, outer,
-                                final, aux, batch.pde_params, batch.T, grad_scale=1.0 / self.bsize,
-                                out_g_theta=self._packed[:P], out_g_lrs=self._packed[P:].view(K, P))
+        out = self._rollout_graphed(batch) if self.use_cuda_graph else self._rollout(batch)
         if self.world > 1:
             torch.distributed.all_reduce(self._packed, group=self.group)
         return out
