@@ -31,7 +31,9 @@ namespace tc {
 // expands cvt.rna.tf32.f32 into 4 instructions (add, inf/nan test, select, mask: ncu r01e); the operands here are
 // finite, so the add and the mask suffice.
 TC_DEV float tf32_rn(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
-TC_DEV void split_tf32(float x, float& hi, float& lo) { hi = tf32_rn(x); lo = tf32_rn(x - hi); }
+// lo = x - hi is exact; the tensor core reads only its upper 19 bits (truncation: 2^-21 |x|, far below the 2^-11 of
+// a single tf32 term), so it is stored unrounded
+TC_DEV void split_tf32(float x, float& hi, float& lo) { hi = tf32_rn(x); lo = x - hi; }
 
 constexpr int WG_QR = 16;                    // rows per pipeline step
 constexpr int WG_GROUP = 8;                  // steps per accumulator generation (128 rows)
