@@ -167,7 +167,7 @@ def run_reference(args, wl, name):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb = cpu_baseline(wl, steps=max(1, args.steps), warmup=min(args.warmup, 1), budget_s=120.0)
+    cb = cpu_baseline(wl, steps=max(1, args.steps), warmup=min(args.warmup, 1), sample_n=min(wl["n"], 4096), budget_s=120.0)
     line = {"impl": "reference", "metric": "maml_outer_steps_per_sec", "value": cb["value"], "unit": "steps/s",
             "n_gpus": args.gpus, "steps": cb["steps_timed"], "warmup": min(args.warmup, 1),
             "ms_per_step": 1e3 / cb["value"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -350,7 +350,8 @@ def run_ours(args, wl, name):
         "losses_finite": finite,
     }
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(wl, steps=4, warmup=1)     # ~20 s of host work on the bounded sample
+        # bounded sample: 1 task x 4096+4096 points, 4 timed repetitions after a warm-up (10-20 s on the box's cores)
+        line["cpu_baseline"] = cpu_baseline(wl, steps=4, warmup=1, sample_n=min(wl["n"], 4096), budget_s=40.0)
     sys.stdout.flush()
     os.dup2(stdout_fd, 1)
     print(json.dumps(line), flush=True)
