@@ -148,6 +148,25 @@ int mpde_adam_step(float* x, const float* g, float* m, float* v, int64_t n, int 
 /*   x -= lr * g_eff   (flax.optim.Momentum beta=0 / "sgd", src/util/trainer_util.py:606-608) */
 int mpde_sgd_step(float* x, const float* g, int64_t n, float lr, const float* sumsq, float clip, void* stream);
 
+/* out[i] = scale * SUM_t x[t][i] in fixed task order: the task mean of src/nets/maml.py:231 / src/nets/leap.py:186
+ * (scale = 1/T_global on every rank, then the ranks all-reduce) and the task SUM of the fine-tune batch loss
+ * (src/nn_pde_maml.py:110-124, scale = 1). */
+int mpde_task_sum(float* out, const float* x, int T, int64_t P, float scale, void* stream);
+
+/* Fused outer step: one launch replaces the reference's
+ *   meta_grad_norm = sqrt(sum(g_theta^2));  (g_theta, g_lrs) *= clip / norm  if norm > clip   (the lr-tree grads are
+ *   rescaled by the MODEL-grad norm too: src/maml_pde.py:210-222);  optimizer.apply_gradient(g_theta)
+ *   (flax Adam, or Momentum beta 0 when optimizer == 0; src/util/trainer_util.py:593-612);
+ *   lr_opt_update(step, g_lrs, lr_opt_state)  (jax.experimental.optimizers.adam, src/maml_pde.py:150,225).
+ * g_packed = [g_theta (n_theta) | g_lrs (n_lrs)] is the buffer the ranks all-reduce.  n_lrs = 0: LEAP
+ * (src/leap_pde.py:180-194) and the fine-tune step (src/nn_pde_maml.py:150-169).  t_theta / t_lrs are the 1-based
+ * Adam step counts.  sumsq_out [1] (optional) receives sum(g_theta^2) before clipping.  Deterministic: every CTA
+ * computes the norm in the same fixed order. */
+int mpde_outer_step(float* theta, int64_t n_theta, float* lrs, int64_t n_lrs, const float* g_packed, float* m_theta,
+                    float* v_theta, float* m_lrs, float* v_lrs, int optimizer, int t_theta, float lr_theta, float b1,
+                    float b2, float eps, int t_lrs, float lr_lrs, float b1_lrs, float b2_lrs, float eps_lrs, float clip,
+                    float* sumsq_out, void* stream);
+
 /* ---- R: task-batched MAML outer gradient (src/nets/maml.py:100-233) -----
  * Forward sweep of K inner SGD steps per task, reverse sweep of K Hessian-vector products
  * (SURVEY.md 9.4).  Points are pre-sampled by the caller (the plugin's samplers):

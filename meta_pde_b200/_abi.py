@@ -79,6 +79,10 @@ SIGNATURES = {
     "mpde_adam_step": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, _P,
                                  C.c_float, _P]),
     "mpde_sgd_step": (C.c_int, [_P, _P, C.c_int64, C.c_float, _P, C.c_float, _P]),
+    "mpde_task_sum": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_float, _P]),
+    "mpde_outer_step": (C.c_int, [_P, C.c_int64, _P, C.c_int64, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_float,
+                                  C.c_float, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                  C.c_float, _P, _P]),
     "mpde_maml_workspace_bytes": (C.c_size_t, [C.POINTER(NetDesc), C.POINTER(PdeDesc), C.POINTER(PdeDesc),
                                                C.POINTER(MamlCfg), C.c_int]),
     "mpde_maml_outer": (C.c_int, [C.POINTER(NetDesc), C.POINTER(PdeDesc), C.POINTER(PdeDesc), C.POINTER(MamlCfg),
@@ -129,7 +133,28 @@ class Kernels:
     def __init__(self, abi, device):
         self.abi = abi
         self.device = torch.device(device)
-        self._ws = None  # grow-only workspace cache
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self._ws = None       # grow-only workspace cache (single stream: see workspace())
+        self._ws_gen = 0      # bumped whenever the cached workspace is reallocated
+        self._sumsq_ws = None
+        if self.device.type == "cuda":
+            # every ABI entry point is called with this object's device current: the library sets per-device kernel
+            # attributes and launches on the caller's stream, which must belong to the current device
+            pure = ("mpde_param_count", "mpde_num_point_sets", "mpde_num_terms", "mpde_num_pde_params", "mpde_status_string",
+                    "mpde_launch_count", "mpde_backend", "mpde_prof_enable", "mpde_sumsq_workspace_bytes")
+            for name in SIGNATURES:
+                if name not in pure:       # includes the *_workspace_bytes planners: they query the current device
+                    setattr(self, "_" + name, self._guarded(getattr(abi, name)))
+        self._fn = lambda name: getattr(self, "_" + name, None) or getattr(self.abi, name)
+
+    def _guarded(self, fn):
+        dev = self.device
+
+        def call(*args):
+            with torch.cuda.device(dev):
+                return fn(*args)
+        return call
 
     # ---------------------------------------------------------------- helpers
     def _check(self, rc):
@@ -146,9 +171,31 @@ class Kernels:
             return None
         if not torch.is_tensor(x) or x.dtype != torch.float32 or x.device.type != self.device.type or not x.is_contiguous():
             raise MpdeError(f"{name}: expected a contiguous float32 tensor on {self.device}")
+        if self.device.type == "cuda" and x.device.index != self.device.index:
+            raise MpdeError(f"{name}: tensor lives on {x.device}, this Kernels object drives {self.device}")
         return x
 
-    def workspace(self, nbytes):
+    def _eval_bytes(self, net, pd, T, mode):
+        nb = self._fn("mpde_workspace_bytes")(C.byref(net), C.byref(pd), T, mode)
+        if nb == 0:
+            raise MpdeError("metapde_b200: unsupported network / invalid problem description (workspace size 0)")
+        return nb
+
+    def _prm(self, pde_params, pde, T):
+        prm = self._t(pde_params, "pde_params")
+        if prm.shape != (T, PDE_NPRM[pde]):
+            raise MpdeError(f"pde_params: expected [T={T}, {PDE_NPRM[pde]}], got {tuple(prm.shape)}")
+        return prm
+
+    def workspace(self, nbytes, private=None):
+        """The cached grow-only workspace of this object, or ``private`` (a caller-owned uint8 tensor) when given.
+        The cached buffer is shared by every call on this object and is therefore SINGLE-STREAM: callers that record
+        calls into a CUDA graph or use several streams pass their own ``private`` buffer (MamlTrainer does).  Growing
+        frees the old buffer after a device synchronise; ``workspace_generation`` changes when that happens."""
+        if private is not None:
+            if private.numel() < nbytes:
+                raise MpdeError(f"private workspace of {private.numel()} bytes, {nbytes} needed")
+            return private
         if self._ws is None or self._ws.numel() < nbytes:
             # release the old buffer first: at C5 size the tensor-core path's spills take 60-115 GB, and old + new
             # would not fit in the 180 GB (the stream is synchronised so that no launch still uses the old one)
@@ -157,7 +204,12 @@ class Kernels:
                 self._ws = None
                 torch.cuda.empty_cache()
             self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            self._ws_gen += 1
         return self._ws
+
+    @property
+    def workspace_generation(self):
+        return self._ws_gen
 
     def net_desc(self, num_layers, layer_size, out_dim, omega, log_scale=True, in_dim=2):
         return NetDesc(int(num_layers), int(layer_size), int(in_dim), int(out_dim), float(omega), int(bool(log_scale)))
@@ -206,19 +258,13 @@ class Kernels:
         theta, st = self._theta(theta, T, P)
         pts, n_points = self.points_struct(pde, sets, T)
         pd = self.pde_desc(pde, bc_weight, n_points)
-        prm = self._t(pde_params, "pde_params")
-        if prm.shape != (T, PDE_NPRM[pde]):
-            raise MpdeError(f"pde_params: expected [T={T}, {PDE_NPRM[pde]}], got {tuple(prm.shape)}")
+        prm = self._prm(pde_params, pde, T)
         nt = len(PDE_TERMS[pde])
         loss = torch.empty(T, dtype=torch.float32, device=self.device)
         terms = torch.empty(T, nt, dtype=torch.float32, device=self.device)
         res = torch.empty(T, n_points[-1], dtype=torch.float32, device=self.device) if want_residual else None
-        nb = self.abi.mpde_workspace_bytes(C.byref(net), C.byref(pd), T, MODE_LOSS)
-        if nb == 0:
-            self._check(self.abi.mpde_loss(C.byref(net), C.byref(pd), T, _ptr(theta), st, C.byref(pts), _ptr(prm),
-                                           _ptr(loss), _ptr(terms), _ptr(res), None, 0, self._stream()))
-        ws = self.workspace(nb)
-        self._check(self.abi.mpde_loss(C.byref(net), C.byref(pd), T, _ptr(theta), st, C.byref(pts), _ptr(prm),
+        ws = self.workspace(self._eval_bytes(net, pd, T, MODE_LOSS))
+        self._check(self._fn("mpde_loss")(C.byref(net), C.byref(pd), T, _ptr(theta), st, C.byref(pts), _ptr(prm),
                                        _ptr(loss), _ptr(terms), _ptr(res), _ptr(ws), ws.numel(), self._stream()))
         return (loss, terms, res) if want_residual else (loss, terms)
 
@@ -227,14 +273,13 @@ class Kernels:
         theta, st = self._theta(theta, T, P)
         pts, n_points = self.points_struct(pde, sets, T)
         pd = self.pde_desc(pde, bc_weight, n_points)
-        prm = self._t(pde_params, "pde_params")
+        prm = self._prm(pde_params, pde, T)
         nt = len(PDE_TERMS[pde])
         loss = torch.empty(T, dtype=torch.float32, device=self.device)
         terms = torch.empty(T, nt, dtype=torch.float32, device=self.device)
         grad = torch.empty(T, P, dtype=torch.float32, device=self.device)
-        nb = self.abi.mpde_workspace_bytes(C.byref(net), C.byref(pd), T, MODE_GRAD)
-        ws = self.workspace(max(nb, 1))
-        self._check(self.abi.mpde_loss_grad(C.byref(net), C.byref(pd), T, _ptr(theta), st, C.byref(pts), _ptr(prm),
+        ws = self.workspace(self._eval_bytes(net, pd, T, MODE_GRAD))
+        self._check(self._fn("mpde_loss_grad")(C.byref(net), C.byref(pd), T, _ptr(theta), st, C.byref(pts), _ptr(prm),
                                             _ptr(loss), _ptr(terms), _ptr(grad), _ptr(ws), ws.numel(), self._stream()))
         return loss, terms, grad
 
@@ -250,15 +295,14 @@ class Kernels:
             raise MpdeError(f"v: expected [P] or [T, P], got {tuple(v.shape)}")
         pts, n_points = self.points_struct(pde, sets, T)
         pd = self.pde_desc(pde, bc_weight, n_points)
-        prm = self._t(pde_params, "pde_params")
+        prm = self._prm(pde_params, pde, T)
         nt = len(PDE_TERMS[pde])
         loss = torch.empty(T, dtype=torch.float32, device=self.device)
         terms = torch.empty(T, nt, dtype=torch.float32, device=self.device)
         grad = torch.empty(T, P, dtype=torch.float32, device=self.device) if want_grad else None
         hv = torch.empty(T, P, dtype=torch.float32, device=self.device)
-        nb = self.abi.mpde_workspace_bytes(C.byref(net), C.byref(pd), T, MODE_HVP)
-        ws = self.workspace(max(nb, 1))
-        self._check(self.abi.mpde_loss_hvp(C.byref(net), C.byref(pd), T, _ptr(theta), st, _ptr(v), vst, C.byref(pts),
+        ws = self.workspace(self._eval_bytes(net, pd, T, MODE_HVP))
+        self._check(self._fn("mpde_loss_hvp")(C.byref(net), C.byref(pd), T, _ptr(theta), st, _ptr(v), vst, C.byref(pts),
                                            _ptr(prm), _ptr(loss), _ptr(terms), _ptr(grad), _ptr(hv), _ptr(ws),
                                            ws.numel(), self._stream()))
         return loss, terms, grad, hv
@@ -272,9 +316,9 @@ class Kernels:
         else:
             n, cst = coords.shape[0], 0
         out = torch.empty(T, n, net.out_dim, dtype=torch.float32, device=self.device)
-        nb = self.abi.mpde_field_eval_workspace_bytes(C.byref(net), T)
+        nb = self._fn("mpde_field_eval_workspace_bytes")(C.byref(net), T)
         ws = self.workspace(max(nb, 1))
-        self._check(self.abi.mpde_field_eval(C.byref(net), T, _ptr(theta), st, _ptr(coords), cst, n, _ptr(out),
+        self._check(self._fn("mpde_field_eval")(C.byref(net), T, _ptr(theta), st, _ptr(coords), cst, n, _ptr(out),
                                              _ptr(ws), ws.numel(), self._stream()))
         return out
 
@@ -286,7 +330,7 @@ class Kernels:
         gn = torch.empty(T, dtype=torch.float32, device=self.device)
         a_t = alpha if torch.is_tensor(alpha) else None
         a_s = 1.0 if torch.is_tensor(alpha) else float(alpha)
-        self._check(self.abi.mpde_maml_inner_update(T, P, _ptr(theta), st, _ptr(self._t(grad, "grad")),
+        self._check(self._fn("mpde_maml_inner_update")(T, P, _ptr(theta), st, _ptr(self._t(grad, "grad")),
                                                     _ptr(self._t(a_t, "alpha")), a_s, int(softplus_lrs),
                                                     float(inner_lr), float(clip), _ptr(out), _ptr(gn), self._stream()))
         return out, gn
@@ -297,7 +341,7 @@ class Kernels:
     def prof_read(self, mode):
         """-> (total_ms, launches) of the jet-kernel launches of ``mode`` since the last read."""
         ms, n = C.c_double(0.0), C.c_int64(0)
-        self._check(self.abi.mpde_prof_read(int(mode), C.byref(ms), C.byref(n)))
+        self._check(self._fn("mpde_prof_read")(int(mode), C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
     def launch_count(self):
@@ -306,18 +350,47 @@ class Kernels:
     def sumsq(self, x):
         out = torch.empty(1, dtype=torch.float32, device=self.device)
         nb = self.abi.mpde_sumsq_workspace_bytes(x.numel())
-        ws = torch.empty(int(nb), dtype=torch.uint8, device=self.device)
-        self._check(self.abi.mpde_sumsq(_ptr(self._t(x, "x")), x.numel(), _ptr(out), _ptr(ws), ws.numel(), self._stream()))
+        if self._sumsq_ws is None or self._sumsq_ws.numel() < nb:
+            self._sumsq_ws = torch.empty(int(nb), dtype=torch.uint8, device=self.device)
+        ws = self._sumsq_ws
+        self._check(self._fn("mpde_sumsq")(_ptr(self._t(x, "x")), x.numel(), _ptr(out), _ptr(ws), ws.numel(), self._stream()))
         return out
 
     def adam_step(self, x, g, m, v, t, lr, b1, b2, eps=1e-8, sumsq=None, clip=0.0):
-        self._check(self.abi.mpde_adam_step(_ptr(self._t(x, "x")), _ptr(self._t(g, "g")), _ptr(self._t(m, "m")),
+        self._check(self._fn("mpde_adam_step")(_ptr(self._t(x, "x")), _ptr(self._t(g, "g")), _ptr(self._t(m, "m")),
                                             _ptr(self._t(v, "v")), x.numel(), int(t), float(lr), float(b1), float(b2),
                                             float(eps), _ptr(sumsq), float(clip), self._stream()))
 
     def sgd_step(self, x, g, lr, sumsq=None, clip=0.0):
-        self._check(self.abi.mpde_sgd_step(_ptr(self._t(x, "x")), _ptr(self._t(g, "g")), x.numel(), float(lr),
+        self._check(self._fn("mpde_sgd_step")(_ptr(self._t(x, "x")), _ptr(self._t(g, "g")), x.numel(), float(lr),
                                            _ptr(sumsq), float(clip), self._stream()))
+
+    def task_sum(self, x, scale=1.0, out=None):
+        """[T, P] -> [P]: scale * sum over tasks, fixed order (maml.py:231 with scale = 1/T)."""
+        T, P = x.shape
+        out = torch.empty(P, dtype=torch.float32, device=self.device) if out is None else out
+        self._check(self._fn("mpde_task_sum")(_ptr(self._t(out, "out")), _ptr(self._t(x, "x")), int(T), int(P), float(scale),
+                                              self._stream()))
+        return out
+
+    def outer_step(self, theta, g_packed, m_theta, v_theta, t_theta, lr_theta, b1, b2, eps=1e-8, clip=1e14,
+                   optimizer="adam", lrs=None, m_lrs=None, v_lrs=None, t_lrs=1, lr_lrs=0.0, b1_lrs=0.9, b2_lrs=0.99,
+                   eps_lrs=1e-8, out=None):
+        """One launch: ||g_theta||, clip of [g_theta | g_lrs] by it, optimizer step on theta, jax-adam step on the lr
+        tree (src/maml_pde.py:210-225).  Returns the device scalar sum(g_theta^2)."""
+        n_theta = theta.numel()
+        n_lrs = 0 if lrs is None else lrs.numel()
+        if g_packed.numel() != n_theta + n_lrs:
+            raise MpdeError(f"g_packed: expected {n_theta + n_lrs} floats, got {g_packed.numel()}")
+        out = torch.empty(1, dtype=torch.float32, device=self.device) if out is None else out
+        adam = optimizer != "sgd"
+        self._check(self._fn("mpde_outer_step")(
+            _ptr(self._t(theta, "theta")), n_theta, _ptr(self._t(lrs, "lrs")), n_lrs, _ptr(self._t(g_packed, "g_packed")),
+            _ptr(self._t(m_theta, "m_theta") if adam else None), _ptr(self._t(v_theta, "v_theta") if adam else None),
+            _ptr(self._t(m_lrs, "m_lrs")), _ptr(self._t(v_lrs, "v_lrs")), 1 if adam else 0, int(t_theta), float(lr_theta),
+            float(b1), float(b2), float(eps), int(t_lrs), float(lr_lrs), float(b1_lrs), float(b2_lrs), float(eps_lrs),
+            float(clip), _ptr(out), self._stream()))
+        return out
 
     # ---------------------------------------------------------------- rollouts
     def _points_array(self, pde, list_of_sets, T):
@@ -332,8 +405,15 @@ class Kernels:
                 raise MpdeError("all inner steps must use the same number of points per set")
         return arr, n_points
 
+    def maml_workspace_bytes(self, net, pde, bc_weight, cfg, n_inner, n_outer, T):
+        mc = MamlCfg(int(cfg["inner_steps"]), float(cfg["inner_lr"]), float(cfg["inner_grad_clip"]),
+                     int(bool(cfg["softplus_lrs"])), float(cfg["outer_loss_decay"]))
+        pdi, pdo = self.pde_desc(pde, bc_weight, n_inner), self.pde_desc(pde, bc_weight, n_outer)
+        return self._fn("mpde_maml_workspace_bytes")(C.byref(net), C.byref(pdi), C.byref(pdo), C.byref(mc), T)
+
     def maml_outer(self, net, pde, bc_weight, cfg, theta0, inner_lrs, inner_sets, outer_sets, final_sets, aux_sets,
-                   pde_params, T, grad_scale=None, want_theta_final=False, out_g_theta=None, out_g_lrs=None):
+                   pde_params, T, grad_scale=None, want_theta_final=False, out_g_theta=None, out_g_lrs=None,
+                   workspace=None):
         """cfg: dict(inner_steps, inner_lr, inner_grad_clip, softplus_lrs, outer_loss_decay).
         inner_sets / outer_sets: K lists of point tensors (ABI order); final_sets / aux_sets: one list each."""
         P = self.param_count(net)
@@ -349,7 +429,7 @@ class Kernels:
             raise MpdeError("final points must match the inner sizes and aux points the outer sizes")
         pdi = self.pde_desc(pde, bc_weight, n_in)
         pdo = self.pde_desc(pde, bc_weight, n_out)
-        prm = self._t(pde_params, "pde_params")
+        prm = self._prm(pde_params, pde, T)
         lrs = self._t(inner_lrs, "inner_lrs")
         nt = len(PDE_TERMS[pde])
         dev = self.device
@@ -365,10 +445,12 @@ class Kernels:
         meta = torch.empty(T, dtype=torch.float32, device=dev)
         aux = torch.empty(T, nt, dtype=torch.float32, device=dev)
         thf = torch.empty(T, P, dtype=torch.float32, device=dev) if want_theta_final else None
-        nb = self.abi.mpde_maml_workspace_bytes(C.byref(net), C.byref(pdi), C.byref(pdo), C.byref(mc), T)
-        ws = self.workspace(max(nb, 1))
+        nb = self._fn("mpde_maml_workspace_bytes")(C.byref(net), C.byref(pdi), C.byref(pdo), C.byref(mc), T)
+        if nb == 0:
+            raise MpdeError("metapde_b200: unsupported network / invalid MAML configuration (workspace size 0)")
+        ws = self.workspace(nb, private=workspace)
         gs = (1.0 / T) if grad_scale is None else float(grad_scale)
-        self._check(self.abi.mpde_maml_outer(C.byref(net), C.byref(pdi), C.byref(pdo), C.byref(mc), T, _ptr(theta0),
+        self._check(self._fn("mpde_maml_outer")(C.byref(net), C.byref(pdi), C.byref(pdo), C.byref(mc), T, _ptr(theta0),
                                              _ptr(lrs), ipts, opts, C.byref(fpts), C.byref(apts), _ptr(prm), gs,
                                              _ptr(g_theta), _ptr(g_lrs), _ptr(losses), _ptr(meta), _ptr(aux), _ptr(thf),
                                              _ptr(ws), ws.numel(), self._stream()))
@@ -383,19 +465,19 @@ class Kernels:
         ipts, n_in = self._points_array(pde, inner_sets, T)
         fpts, n_f = self.points_struct(pde, final_sets, T)
         pdi = self.pde_desc(pde, bc_weight, n_in)
-        prm = self._t(pde_params, "pde_params")
+        prm = self._prm(pde_params, pde, T)
         lrs = self._t(inner_lrs, "inner_lrs")
         thf = torch.empty(T, P, dtype=torch.float32, device=self.device)
         losses = torch.empty(T, K + 1, dtype=torch.float32, device=self.device)
-        nb = self.abi.mpde_maml_workspace_bytes(C.byref(net), C.byref(pdi), None, C.byref(mc), T)
+        nb = self._fn("mpde_maml_workspace_bytes")(C.byref(net), C.byref(pdi), None, C.byref(mc), T)
         ws = self.workspace(max(nb, 1))
-        self._check(self.abi.mpde_maml_adapt(C.byref(net), C.byref(pdi), C.byref(mc), T, _ptr(self._t(theta0, "theta0")),
+        self._check(self._fn("mpde_maml_adapt")(C.byref(net), C.byref(pdi), C.byref(mc), T, _ptr(self._t(theta0, "theta0")),
                                              _ptr(lrs), ipts, C.byref(fpts), _ptr(prm), _ptr(thf), _ptr(losses),
                                              _ptr(ws), ws.numel(), self._stream()))
         return thf, losses
 
     def leap_outer(self, net, pde, bc_weight, cfg, theta0, loss0_sets, step_sets, new_sets, pde_params, T,
-                   grad_scale=None, want_theta_final=False):
+                   grad_scale=None, want_theta_final=False, out_meta_grad=None):
         """cfg: dict(inner_steps, inner_lr, inner_grad_clip, norm, loss_in_distance, stabilize, inner_opt, beta1, beta2, eps)."""
         P = self.param_count(net)
         K = int(cfg["inner_steps"])
@@ -409,14 +491,16 @@ class Kernels:
         if not (n0 == n1 == n2):
             raise MpdeError("LEAP point sets must all have the same sizes")
         pd = self.pde_desc(pde, bc_weight, n0)
-        prm = self._t(pde_params, "pde_params")
-        g = torch.empty(P, dtype=torch.float32, device=self.device)
+        prm = self._prm(pde_params, pde, T)
+        g = self._t(out_meta_grad, "out_meta_grad") if out_meta_grad is not None else torch.empty(P, dtype=torch.float32, device=self.device)
+        if g.numel() != P:
+            raise MpdeError(f"out_meta_grad: expected {P} floats")
         losses = torch.empty(T, K + 1, dtype=torch.float32, device=self.device)
         thf = torch.empty(T, P, dtype=torch.float32, device=self.device) if want_theta_final else None
-        nb = self.abi.mpde_leap_workspace_bytes(C.byref(net), C.byref(pd), C.byref(lc), T)
+        nb = self._fn("mpde_leap_workspace_bytes")(C.byref(net), C.byref(pd), C.byref(lc), T)
         ws = self.workspace(max(nb, 1))
         gs = (1.0 / T) if grad_scale is None else float(grad_scale)
-        self._check(self.abi.mpde_leap_outer(C.byref(net), C.byref(pd), C.byref(lc), T, _ptr(self._t(theta0, "theta0")),
+        self._check(self._fn("mpde_leap_outer")(C.byref(net), C.byref(pd), C.byref(lc), T, _ptr(self._t(theta0, "theta0")),
                                              C.byref(l0), sp, npn, _ptr(prm), gs, _ptr(g), _ptr(losses), _ptr(thf),
                                              _ptr(ws), ws.numel(), self._stream()))
         return {"meta_grad": g, "losses": losses, "theta_final": thf}

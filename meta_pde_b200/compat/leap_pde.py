@@ -34,16 +34,17 @@ def train_step(key, leap_def, optimizer):
     """src/leap_pde.py:175-195 -> (optimizer, losses, meta_grad_norm)"""
     K = ops.kernels(optimizer.target.theta.device)
     meta_grad, losses = leap.multi_task_grad_and_losses(leap_def, key, optimizer.target)
-    sumsq = K.sumsq(meta_grad.theta)
     od = optimizer.optimizer_def
-    x = optimizer.target.theta.detach().clone()
-    if isinstance(od, Adam):
-        m, v, t = optimizer.state["m"].clone(), optimizer.state["v"].clone(), optimizer.state["step"] + 1
-        K.adam_step(x, meta_grad.theta, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, sumsq, FLAGS.grad_clip)
+    x = optimizer.target.theta.detach().clone().contiguous()
+    g = meta_grad.theta.detach().contiguous().view(-1)
+    t = optimizer.state["step"] + 1
+    if isinstance(od, Adam):          # fused ||g||, clip, Adam (mpde_outer_step with no lr tree)
+        m, v = optimizer.state["m"].clone(), optimizer.state["v"].clone()
+        sumsq = K.outer_step(x, g, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, FLAGS.grad_clip, "adam")
         state = {"step": t, "m": m, "v": v}
     else:
-        K.sgd_step(x, meta_grad.theta, od.learning_rate, sumsq, FLAGS.grad_clip)
-        state = {"step": optimizer.state["step"] + 1}
+        sumsq = K.outer_step(x, g, None, None, t, od.learning_rate, 0.0, 0.0, 1e-8, FLAGS.grad_clip, "sgd")
+        state = {"step": t}
     return type(optimizer)(od, field.Model(optimizer.target.module, x), state), losses, torch.sqrt(sumsq)
 
 

@@ -180,11 +180,16 @@ def _fused_outer(maml_def, tasks, initial_model, inner_lrs, K, scale):
         prms.append(pde.abi_params(inner_fn.params))
     prm = torch.stack(prms).to(dev).contiguous()
     lrs = inner_lrs.theta.contiguous() if inner_lrs is not None else None
+    # one packed buffer [g_theta | g_lrs]: the layout of the all-reduce and of the fused outer step (mpde_outer_step)
+    P = initial_model.theta.numel()
+    packed = torch.empty((1 + (K if lrs is not None else 0)) * P, dtype=torch.float32, device=dev)
     out = K_.maml_outer(initial_model.net_desc(K_), pde.name, inner_fn0.bc_weight, _cfg(maml_def, K),
                         initial_model.theta.detach().contiguous(), lrs, [_stack_points(pde, p) for p in inner_pts],
                         [_stack_points(pde, p) for p in outer_pts], _stack_points(pde, final_pts),
-                        _stack_points(pde, aux_pts), prm, T, grad_scale=scale)
+                        _stack_points(pde, aux_pts), prm, T, grad_scale=scale, out_g_theta=packed[:P],
+                        out_g_lrs=packed[P:].view(K, P) if lrs is not None else None)
     g_model = Model(initial_model.module, out["g_theta"])
+    g_model.packed = packed
     grads = (g_model, Model(initial_model.module, out["g_lrs"])) if inner_lrs is not None else g_model
     aux = {n: out["aux_terms"][:, i] for i, n in enumerate(PDE_TERMS[pde.name])}
     return grads, out["losses"], (out["meta_losses"], aux)

@@ -40,20 +40,27 @@ def train_step(step, key, maml_def, optimizer, inner_lrs, lr_state):
     """src/maml_pde.py:203-226.  Returns (optimizer, inner_lrs, losses, meta_losses, meta_grad_norm)."""
     K = ops.kernels(optimizer.target.theta.device)
     (g_model, g_lrs), losses, meta_losses = maml.multi_task_grad_and_losses(maml_def, key, optimizer.target, inner_lrs)
-    sumsq = K.sumsq(g_model.theta)                       # the norm of the MODEL grads only (quirk 1) ...
-    x = optimizer.target.theta.detach().clone()
+    packed = getattr(g_model, "packed", None)            # fused route: [g_theta | g_lrs] already contiguous
+    if packed is None:
+        packed = torch.cat([g_model.theta.reshape(-1), g_lrs.theta.reshape(-1)]).contiguous()
+    # One launch (mpde_outer_step): the norm of the MODEL grads only (quirk 1) rescales the lr-tree grads too, the outer
+    # optimizer steps theta, jax.experimental.optimizers.adam at index `step` steps the lr tree (maml_pde.py:210-225)
+    x = optimizer.target.theta.detach().clone().contiguous()
+    lrs = inner_lrs.theta.detach().clone().contiguous()
     od = optimizer.optimizer_def
+    t = optimizer.state["step"] + 1
     if isinstance(od, Adam):
-        m, v, t = optimizer.state["m"].clone(), optimizer.state["v"].clone(), optimizer.state["step"] + 1
-        K.adam_step(x, g_model.theta, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, sumsq, FLAGS.grad_clip)
+        m, v = optimizer.state["m"].clone(), optimizer.state["v"].clone()
+        sumsq = K.outer_step(x, packed, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, FLAGS.grad_clip, "adam",
+                             lrs=lrs.view(-1), m_lrs=lr_state["m"].view(-1), v_lrs=lr_state["v"].view(-1), t_lrs=step + 1,
+                             lr_lrs=FLAGS.lr_inner_lr)
         state = {"step": t, "m": m, "v": v}
     else:
-        K.sgd_step(x, g_model.theta, od.learning_rate, sumsq, FLAGS.grad_clip)
-        state = {"step": optimizer.state["step"] + 1}
+        sumsq = K.outer_step(x, packed, None, None, t, od.learning_rate, 0.0, 0.0, 1e-8, FLAGS.grad_clip, "sgd",
+                             lrs=lrs.view(-1), m_lrs=lr_state["m"].view(-1), v_lrs=lr_state["v"].view(-1), t_lrs=step + 1,
+                             lr_lrs=FLAGS.lr_inner_lr)
+        state = {"step": t}
     optimizer = type(optimizer)(od, field.Model(optimizer.target.module, x), state)
-    lrs = inner_lrs.theta.detach().clone()               # ... rescales the lr-tree grads too; jax adam at index `step`
-    K.adam_step(lrs.view(-1), g_lrs.theta.contiguous().view(-1), lr_state["m"].view(-1), lr_state["v"].view(-1), step + 1,
-                FLAGS.lr_inner_lr, 0.9, 0.99, 1e-8, sumsq, FLAGS.grad_clip)
     return optimizer, field.Model(inner_lrs.module, lrs), losses, meta_losses, torch.sqrt(sumsq)
 
 

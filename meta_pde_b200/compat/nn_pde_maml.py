@@ -32,23 +32,24 @@ def batch_loss_and_grad(pde, key, model):
     prm = torch.stack(prms).to(model.theta.device).contiguous()
     loss, terms, grad = K.loss_grad(model.net_desc(K), pde.name, FLAGS.bc_weight, model.theta.contiguous(), sets, prm, FLAGS.bsize)
     aux = {n: terms[:, i].mean() for i, n in enumerate(PDE_TERMS[pde.name])}
-    return loss.sum(), aux, grad.sum(dim=0)
+    return loss.sum(), aux, K.task_sum(grad, 1.0)          # grad of the SUM over the bsize tasks (:110-124)
 
 
 def train_step(pde, key, optimizer):
     """src/nn_pde_maml.py:140-171 -> (optimizer, loss, loss_aux, grad_norm)"""
     K = ops.kernels(optimizer.target.theta.device)
     loss, aux, grad = batch_loss_and_grad(pde, key, optimizer.target)
-    sumsq = K.sumsq(grad)
     od = optimizer.optimizer_def
-    x = optimizer.target.theta.detach().clone()
-    if isinstance(od, Adam):
-        m, v, t = optimizer.state["m"].clone(), optimizer.state["v"].clone(), optimizer.state["step"] + 1
-        K.adam_step(x, grad, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, sumsq, FLAGS.grad_clip)
+    x = optimizer.target.theta.detach().clone().contiguous()
+    g = grad.detach().contiguous().view(-1)
+    t = optimizer.state["step"] + 1
+    if isinstance(od, Adam):          # fused ||g||, clip, Adam (mpde_outer_step with no lr tree)
+        m, v = optimizer.state["m"].clone(), optimizer.state["v"].clone()
+        sumsq = K.outer_step(x, g, m, v, t, od.learning_rate, od.beta1, od.beta2, od.eps, FLAGS.grad_clip, "adam")
         state = {"step": t, "m": m, "v": v}
     else:
-        K.sgd_step(x, grad, od.learning_rate, sumsq, FLAGS.grad_clip)
-        state = {"step": optimizer.state["step"] + 1}
+        sumsq = K.outer_step(x, g, None, None, t, od.learning_rate, 0.0, 0.0, 1e-8, FLAGS.grad_clip, "sgd")
+        state = {"step": t}
     return type(optimizer)(od, field.Model(optimizer.target.module, x), state), loss, aux, torch.sqrt(sumsq)
 
 

@@ -20,14 +20,15 @@ int device_sm_count() {
 #ifdef MPDE_EMU
   return 4;
 #else
-  static int n = 0;
-  static std::once_flag once;
-  std::call_once(once, []() {
-    int dev = 0;
-    cudaGetDevice(&dev);
+  static std::atomic<int> cache[PerDeviceOnce::MAXDEV];   // zero-initialised; per device
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= PerDeviceOnce::MAXDEV) return 148;
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n < 1) {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n < 1) n = 148;
-  });
+    cache[dev].store(n, std::memory_order_relaxed);
+  }
   return n;
 #endif
 }
@@ -36,13 +37,15 @@ int device_sm_count() {
 #ifndef MPDE_EMU
 struct ProfState {
   std::mutex mu;
-  bool on = false;
+  std::atomic<bool> on{false};
   std::vector<cudaEvent_t> ev[4];   // pairs: [2i] start, [2i+1] stop; slot 3 = tc_wgrad_kernel launches
   size_t used[4] = {0, 0, 0, 0};
 };
 static ProfState g_prof;
 static bool prof_begin(int mode, void* stream, cudaEvent_t* stop) {
-  if (!g_prof.on) return false;
+  if (!g_prof.on.load(std::memory_order_relaxed)) return false;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;   // events cannot be recorded into a capturing stream
+  if (cudaStreamIsCapturing((cudaStream_t)stream, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return false;
   std::lock_guard<std::mutex> lk(g_prof.mu);
   auto& v = g_prof.ev[mode];
   if (g_prof.used[mode] + 2 > v.size()) {
@@ -614,6 +617,34 @@ int mpde_adam_step(float* x, const float* g, float* m, float* v, int64_t n, int 
 int mpde_sgd_step(float* x, const float* g, int64_t n, float lr, const float* sumsq, float clip, void* stream) {
   if (!x || !g || n < 1) return MPDE_INVALID_ARG;
   return launch_simple(sgd_kernel, grid_for(n), 1, 256, 0, stream, x, g, (long long)n, lr, sumsq, clip);
+}
+
+int mpde_task_sum(float* out, const float* x, int T, int64_t P, float scale, void* stream) {
+  if (!out || !x || T < 1 || P < 1) return MPDE_INVALID_ARG;
+  return launch_simple(task_sum_kernel, grid_for(P), 1, 256, 0, stream, out, x, T, (long long)P, scale);
+}
+
+int mpde_outer_step(float* theta, int64_t n_theta, float* lrs, int64_t n_lrs, const float* g_packed, float* m_theta,
+                    float* v_theta, float* m_lrs, float* v_lrs, int optimizer, int t_theta, float lr_theta, float b1,
+                    float b2, float eps, int t_lrs, float lr_lrs, float b1_lrs, float b2_lrs, float eps_lrs, float clip,
+                    float* sumsq_out, void* stream) {
+  if (!theta || !g_packed || n_theta < 1 || n_lrs < 0 || t_theta < 1) return MPDE_INVALID_ARG;
+  if (optimizer != 0 && optimizer != 1) return MPDE_INVALID_ARG;
+  if (optimizer == 1 && (!m_theta || !v_theta)) return MPDE_INVALID_ARG;
+  if (n_lrs > 0 && (!lrs || !m_lrs || !v_lrs || t_lrs < 1)) return MPDE_INVALID_ARG;
+  OuterStepParams p;
+  p.n_theta = n_theta; p.n_lrs = n_lrs; p.theta = theta; p.lrs = lrs; p.g = g_packed;
+  p.m_theta = m_theta; p.v_theta = v_theta; p.m_lrs = m_lrs; p.v_lrs = v_lrs; p.opt = optimizer;
+  p.lr_theta = lr_theta; p.b1 = b1; p.b2 = b2; p.eps = eps;
+  p.bc1 = 1.f - powf(b1, (float)t_theta); p.bc2 = 1.f - powf(b2, (float)t_theta);
+  p.lr_lrs = lr_lrs; p.b1l = b1_lrs; p.b2l = b2_lrs; p.epsl = eps_lrs;
+  p.bc1l = 1.f - powf(b1_lrs, (float)(t_lrs > 0 ? t_lrs : 1)); p.bc2l = 1.f - powf(b2_lrs, (float)(t_lrs > 0 ? t_lrs : 1));
+  p.clip = clip; p.sumsq_out = sumsq_out;
+  // every CTA re-reads g_theta for the norm (L2-resident): keep the grid at two CTAs per SM for large trees
+  int gx = grid_for(n_theta + n_lrs);
+  const int cap = 2 * device_sm_count();
+  if (gx > cap) gx = cap;
+  return launch_simple(outer_step_kernel, gx, 1, 256, 256 * sizeof(float), stream, p);
 }
 
 // ------------------------------------------------------------------ MAML rollout

@@ -352,6 +352,53 @@ MPDE_GLOBAL void sgd_kernel(float* x, const float* g, long long n, float lr, con
   }
 }
 
+// Fused outer step: ||g_theta||_2, clip of the WHOLE packed tree by that norm, optimizer step on
+// theta and Adam step on the lr tree in ONE launch (src/maml_pde.py:210-225; src/leap_pde.py:180-194 and
+// src/nn_pde_maml.py:150-169 with n_lrs = 0).  Every CTA recomputes the norm of g_theta in the same fixed order
+// (thread-strided partial sums, then the block tree): identical bits in every CTA and on every rank, no grid-wide
+// barrier, no float atomics.  g is packed [g_theta (n_theta) | g_lrs (n_lrs)], the layout of the NCCL all-reduce.
+struct OuterStepParams {
+  long long n_theta, n_lrs;
+  float* theta; float* lrs;
+  const float* g;
+  float* m_theta; float* v_theta; float* m_lrs; float* v_lrs;
+  int opt;                                   // 0: SGD (Momentum beta 0), 1: Adam on theta
+  float lr_theta, b1, b2, eps, bc1, bc2;     // theta: flax Adam, bias corrections 1 - b^t
+  float lr_lrs, b1l, b2l, epsl, bc1l, bc2l;  // lr tree: jax.experimental.optimizers.adam at its own step index
+  float clip;
+  float* sumsq_out;                          // [1]: sum(g_theta^2) (meta_grad_norm^2), written by CTA 0
+};
+MPDE_GLOBAL void outer_step_kernel(OuterStepParams p) {
+  float* sh = reinterpret_cast<float*>(mpde_smem());
+  float ss = 0.f;
+  for (long long i = threadIdx.x; i < p.n_theta; i += blockDim.x) ss = fmaf(p.g[i], p.g[i], ss);
+  ss = block_sum(ss, sh);
+  if (blockIdx.x == 0 && threadIdx.x == 0 && p.sumsq_out) p.sumsq_out[0] = ss;
+  const float nrm = sqrtf(ss);
+  const bool clipped = nrm > p.clip;
+  const long long n = p.n_theta + p.n_lrs;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float gi = p.g[i];
+    if (clipped) gi = p.clip * gi / nrm;
+    if (i < p.n_theta) {
+      if (p.opt == 1) {
+        const float mi = p.b1 * p.m_theta[i] + (1.f - p.b1) * gi;
+        const float vi = p.b2 * p.v_theta[i] + (1.f - p.b2) * gi * gi;
+        p.m_theta[i] = mi; p.v_theta[i] = vi;
+        p.theta[i] = p.theta[i] - p.lr_theta * (mi / p.bc1) / (sqrtf(vi / p.bc2) + p.eps);
+      } else {
+        p.theta[i] = p.theta[i] - p.lr_theta * gi;
+      }
+    } else {
+      const long long j = i - p.n_theta;
+      const float mi = p.b1l * p.m_lrs[j] + (1.f - p.b1l) * gi;
+      const float vi = p.b2l * p.v_lrs[j] + (1.f - p.b2l) * gi * gi;
+      p.m_lrs[j] = mi; p.v_lrs[j] = vi;
+      p.lrs[j] = p.lrs[j] - p.lr_lrs * (mi / p.bc1l) / (sqrtf(vi / p.bc2l) + p.epsl);
+    }
+  }
+}
+
 // LEAP inner step for T tasks (leap.py:75-102,190-228): one block per task.
 struct LeapStepParams {
   int P;

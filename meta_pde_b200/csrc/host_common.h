@@ -3,6 +3,7 @@
 #include "compat.cuh"
 #include "pde_kernels.cuh"
 #include <atomic>
+#include <mutex>
 
 namespace mpde {
 
@@ -15,6 +16,22 @@ struct KernelInfo {
 
 extern std::atomic<long long> g_launches;
 int device_sm_count();
+
+#ifndef MPDE_EMU
+// One-time per-DEVICE kernel attributes (cudaFuncSetAttribute is per device: a process that drives several GPUs must
+// set the dynamic shared memory limit on each of them).  run(f) calls f once for the calling thread's current device.
+struct PerDeviceOnce {
+  static constexpr int MAXDEV = 64;
+  std::once_flag flags[MAXDEV];
+  cudaError_t err[MAXDEV];
+  template <class F> cudaError_t run(F&& f) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAXDEV) return cudaErrorInvalidDevice;
+    std::call_once(flags[dev], [&]() { err[dev] = f(); });
+    return err[dev];
+  }
+};
+#endif
 
 // op 0: fill *info; op 1: launch.  One definition per width (inst_w*.cu) so the widths compile in parallel.
 int dispatch_w32(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);

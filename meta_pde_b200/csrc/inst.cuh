@@ -12,11 +12,13 @@ int run_inst(int op, const KParams* p, int gx, int gy, void* stream, KernelInfo*
   const size_t smem = G::smem_bytes(MODE);
   static int occ = 0;
 #ifndef MPDE_EMU
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&]() {
-    attr_err = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (attr_err == cudaSuccess) attr_err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, G::NT, smem);
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.run([&]() {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int o = 0;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kfn, G::NT, smem);
+    if (e == cudaSuccess) occ = o;      // identical on every device of the node (same GPU model)
+    return e;
   });
   if (attr_err != cudaSuccess || occ < 1) return 4;
 #else

@@ -13,10 +13,8 @@ template <int W, int PDE, int MODE>
 static int tc_run_inst(int op, const TcParams* p, int gx, int gy, void* stream, KernelInfo* info) {
   typedef TcGeo<W> G;
   auto kfn = tc_pde_kernel<W, PDE, MODE>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&]() { attr_err = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM); });
-  if (attr_err != cudaSuccess) return 4;
+  static PerDeviceOnce once;
+  if (once.run([&]() { return cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM); }) != cudaSuccess) return 4;
   if (op == 0) {
     info->nt = G::NT; info->smem = G::SMEM; info->occ = 1; info->np = TR / 4;
     return 0;
@@ -51,10 +49,8 @@ template <int W, int PDE>
 static int tc_run_hvp_inst(int op, const HvParams* p, int gx, int gy, void* stream, KernelInfo* info) {
   typedef HvGeo<W> G;
   auto kfn = tc_hvp_kernel<W, PDE>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&]() { attr_err = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM); });
-  if (attr_err != cudaSuccess) return 4;
+  static PerDeviceOnce once;
+  if (once.run([&]() { return cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM); }) != cudaSuccess) return 4;
   if (op == 0) {
     info->nt = G::NT; info->smem = G::SMEM; info->occ = 1; info->np = HR / 4;
     return 0;
@@ -125,13 +121,13 @@ template <int W, bool HV> static void wgrad_launch(const TcWgradParams* p, dim3 
   tc_wgrad_kernel<W, HV><<<grid, dim3(WgGeo<W, HV>::NT, 1, 1), WgGeo<W, HV>::SMEM, (cudaStream_t)stream>>>(*p);
 }
 int tc_launch_wgrad(const TcWgradParams* p, void* stream) {
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&]() {
-    attr_err = wgrad_attr<128, false>();
-    if (attr_err == cudaSuccess) attr_err = wgrad_attr<128, true>();
-    if (attr_err == cudaSuccess) attr_err = wgrad_attr<256, false>();
-    if (attr_err == cudaSuccess) attr_err = wgrad_attr<256, true>();
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.run([&]() {
+    cudaError_t e = wgrad_attr<128, false>();
+    if (e == cudaSuccess) e = wgrad_attr<128, true>();
+    if (e == cudaSuccess) e = wgrad_attr<256, false>();
+    if (e == cudaSuccess) e = wgrad_attr<256, true>();
+    return e;
   });
   if (attr_err != cudaSuccess) return 4;
   g_launches++;

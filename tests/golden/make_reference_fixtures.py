@@ -363,6 +363,13 @@ def main():
     fixture_maml("poisson", 32, 2, 16, 2, 3, seed=22, inner_lr=1e-2, clip=1e-2, decay=0.5)
     fixture_leap("poisson", 32, 2, 16, 2, 3, seed=31, inner_lr=1e-3, clip=1e14)
     fixture_leap("td_burgers", 32, 2, 16, 2, 2, seed=32, inner_lr=1e-3, clip=0.5)
+    # width 128: the tensor-core (tcgen05) kernels + tc_wgrad_kernel, pinned to the reference source directly (round 2)
+    fixture_loss_grad("poisson", 128, 2, 40, 1, seed=13)
+    fixture_loss_grad("hyper_elasticity", 128, 2, 24, 1, seed=14)
+    fixture_loss_grad("td_burgers", 128, 2, 70, 1, seed=15)
+    fixture_maml("poisson", 128, 2, 16, 2, 2, seed=23, inner_lr=1e-2, clip=1e14, decay=0.1)
+    fixture_maml("td_burgers", 128, 2, 70, 2, 2, seed=24, inner_lr=1e-2, clip=1e-2, decay=0.1)
+    fixture_leap("poisson", 128, 2, 16, 2, 2, seed=33, inner_lr=1e-3, clip=1e14)
 
 
 if __name__ == "__main__":

@@ -216,3 +216,139 @@ def check_field_eval(K, W, L, out, n, T, seed=0):
         want = nf_apply(params, out, coords[t].double(), OMEGA)
         e = rel_l2(u[t].cpu(), want)
         assert e < TOL, f"field_eval W={W} out={out}: {e}"
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Outer train steps: the trainers of meta_pde_b200/train.py (rollout kernels +
+# the fused clip/Adam kernel mpde_outer_step) against oracle/meta.py's restatement of
+#   src/maml_pde.py:203-226 (quirk 1: the norm of the MODEL grads rescales the lr-tree grads too; flax Adam on theta,
+#   jax.experimental.optimizers.adam on alpha), src/leap_pde.py:175-195, src/nn_pde_maml.py:140-171.
+# Compared after every step: theta, the alpha tree, Adam moments, meta_grad_norm.  Tolerance 1e-4 (rel-L2); parameter
+# UPDATES (theta_s - theta_0 etc.) with the float32-resolution rule of _tol.
+# ------------------------------------------------------------------------------------------------------------
+def _upd_tol(x_new, x_old):
+    d = (x_new.double() - x_old.double()).norm().item()
+    return max(TOL, 8 * 6e-8 * x_new.double().norm().item() / max(d, 1e-300))
+
+
+def _check_state(name, got, want, got0, errs, bad):
+    """absolute agreement of the state + agreement of its update since the start"""
+    e = rel_l2(got.cpu(), want)
+    errs[name] = max(errs.get(name, 0.0), e)
+    if not e < TOL:
+        bad[name] = e
+    if got0 is not None:
+        eu = rel_l2(got.cpu().double() - got0.double(), want - got0.double())
+        errs[name + "_update"] = max(errs.get(name + "_update", 0.0), eu)
+        if not eu < _upd_tol(want, got0):
+            bad[name + "_update"] = eu
+
+
+def check_maml_train_steps(K, pde, W, L, n, T, K_steps=2, steps=3, inner_lr=1e-2, outer_lr=1e-3, lr_inner_lr=0.5,
+                           grad_clip=1e14, inner_clip=1e14, optimizer="adam", seed=0, use_cuda_graph=False):
+    from meta_pde_b200 import train
+    out = PDE_OUT_DIM[pde]
+    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    P = theta0.numel()
+    tr = train.MamlTrainer(pde, L, W, theta0, bsize=T, inner_steps=K_steps, inner_lr=inner_lr, outer_lr=outer_lr,
+                           lr_inner_lr=lr_inner_lr, inner_grad_clip=inner_clip, grad_clip=grad_clip, optimizer=optimizer,
+                           kernels=K, use_cuda_graph=use_cuda_graph)
+    lf = oracle_loss_fn(pde, W, L, 1.0)
+    ocfg = ometa.MamlCfg(K_steps, inner_lr, inner_clip, True, 0.1)
+    b1, b2 = {"adam": (0.9, 0.99), "rmsprop": (0.0, 0.8), "sgd": (0.9, 0.99)}[optimizer]
+    opt_theta = ometa.FlaxAdam(outer_lr, b1, b2) if optimizer != "sgd" else None
+    opt_lrs = ometa.JaxAdam(lr_inner_lr, 0.9, 0.99)
+    o_theta, o_lrs = theta0.double(), torch.ones(K_steps, P, dtype=torch.float64)
+    st_theta = opt_theta.init(o_theta) if opt_theta else None
+    st_lrs = opt_lrs.init(o_lrs)
+    errs, bad, clipped = {}, {}, []
+    lrs0 = torch.ones(K_steps, P)
+    for step in range(steps):
+        batch = train.synthetic_maml_batch(pde, T, K_steps, n, n, seed=seed + 11 + step)
+        inner, outer, final, aux = batch.views()
+        tasks = [ometa.MamlTask(oracle_params(pde, batch.pde_params, t), [oracle_points(pde, s, t) for s in inner],
+                                [oracle_points(pde, s, t) for s in outer], oracle_points(pde, final, t),
+                                oracle_points(pde, aux, t)) for t in range(T)]
+        losses, meta, auxt, gnorm = tr.train_step(step, batch.to(K.device))
+        if opt_theta:
+            o_theta, o_lrs, st_theta, st_lrs, o_losses, o_meta, o_gn = ometa.maml_train_step(
+                step, ocfg, lf, o_theta, o_lrs, tasks, opt_theta, st_theta, opt_lrs, st_lrs, grad_clip)
+        else:   # "sgd": Momentum(beta 0) on theta (trainer_util.py:606-608)
+            (g_th, g_l), o_losses, o_meta = ometa.maml_multi_task_grad_and_losses(ocfg, lf, o_theta, tasks, o_lrs)
+            o_gn = ometa.global_norm(g_th)
+            g_th, g_l = ometa.clip_by_norm([g_th, g_l], o_gn, grad_clip)
+            o_theta = o_theta - outer_lr * g_th
+            o_lrs, st_lrs = opt_lrs.apply_at(step, o_lrs, g_l, st_lrs)
+        o_theta, o_lrs = o_theta.detach(), o_lrs.detach()
+        clipped.append(bool(o_gn > grad_clip))
+        _check_state("theta", tr.theta, o_theta, theta0, errs, bad)
+        _check_state("inner_lrs", tr.inner_lrs, o_lrs, lrs0, errs, bad)
+        _check_state("meta_grad_norm", gnorm, o_gn.detach().reshape(1), None, errs, bad)
+        _check_state("losses", losses, o_losses, None, errs, bad)
+        _check_state("meta_losses", meta, o_meta[0], None, errs, bad)
+        if opt_theta:
+            _check_state("m_theta", tr.m_theta, st_theta["m"].detach(), None, errs, bad)
+            _check_state("v_theta", tr.v_theta, st_theta["v"].detach(), None, errs, bad)
+        _check_state("m_lrs", tr.m_lrs, st_lrs["m"].detach(), None, errs, bad)
+        _check_state("v_lrs", tr.v_lrs, st_lrs["v"].detach(), None, errs, bad)
+    assert not bad, f"MAML train_step {pde} {L}x{W} ({optimizer}, clip {grad_clip}): {bad} (all: {errs})"
+    return errs, clipped
+
+
+def check_leap_train_steps(K, pde, W, L, n, T, K_steps=3, steps=3, inner_lr=1e-3, outer_lr=1e-3, grad_clip=1e14, seed=0):
+    from meta_pde_b200 import train
+    out = PDE_OUT_DIM[pde]
+    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    tr = train.LeapTrainer(pde, L, W, theta0, bsize=T, inner_steps=K_steps, inner_lr=inner_lr, outer_lr=outer_lr,
+                           grad_clip=grad_clip, kernels=K)
+    lf = oracle_loss_fn(pde, W, L, 1.0)
+    ocfg = ometa.LeapCfg(K_steps, inner_lr, 1e14, True, True, True, "adam")
+    opt = ometa.FlaxAdam(outer_lr, 0.9, 0.99)
+    o_theta = theta0.double()
+    st = opt.init(o_theta)
+    errs, bad, clipped = {}, {}, []
+    for step in range(steps):
+        batch = train.synthetic_point_batch(pde, T, 1 + 2 * K_steps, n, seed=seed + 21 + step)
+        g = batch.views()
+        tasks = [ometa.LeapTask(oracle_params(pde, batch.pde_params, t), oracle_points(pde, g[0], t),
+                                [oracle_points(pde, s, t) for s in g[1:1 + K_steps]],
+                                [oracle_points(pde, s, t) for s in g[1 + K_steps:]]) for t in range(T)]
+        losses, gnorm = tr.train_step(batch.to(K.device))
+        o_theta, st, o_losses, o_gn = ometa.leap_train_step(ocfg, lf, o_theta, tasks, opt, st, grad_clip)
+        o_theta = o_theta.detach()
+        clipped.append(bool(o_gn > grad_clip))
+        _check_state("theta", tr.theta, o_theta, theta0, errs, bad)
+        _check_state("meta_grad_norm", gnorm, o_gn.detach().reshape(1), None, errs, bad)
+        _check_state("losses", losses, o_losses, None, errs, bad)
+        _check_state("m_theta", tr.m_theta, st["m"].detach(), None, errs, bad)
+        _check_state("v_theta", tr.v_theta, st["v"].detach(), None, errs, bad)
+    assert not bad, f"LEAP train_step {pde} {L}x{W} (clip {grad_clip}): {bad} (all: {errs})"
+    return errs, clipped
+
+
+def check_finetune_train_steps(K, pde, W, L, n, T, steps=3, outer_lr=1e-3, grad_clip=1e14, seed=0):
+    from meta_pde_b200 import train
+    out = PDE_OUT_DIM[pde]
+    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    tr = train.FinetuneTrainer(pde, L, W, theta0, bsize=T, outer_lr=outer_lr, grad_clip=grad_clip, kernels=K)
+    lf = oracle_loss_fn(pde, W, L, 1.0)
+    opt = ometa.FlaxAdam(outer_lr, 0.9, 0.99)
+    o_theta = theta0.double()
+    st = opt.init(o_theta)
+    errs, bad, clipped = {}, {}, []
+    for step in range(steps):
+        batch = train.synthetic_point_batch(pde, T, 1, n, seed=seed + 31 + step)
+        (sets,) = batch.views()
+        ob = [(oracle_points(pde, sets, t), oracle_params(pde, batch.pde_params, t)) for t in range(T)]
+        loss, terms, gnorm = tr.train_step(batch.to(K.device))
+        o_theta, st, o_loss, o_aux, o_gn = ometa.finetune_train_step(lf, o_theta, ob, opt, st, grad_clip)
+        o_theta = o_theta.detach()
+        clipped.append(bool(o_gn > grad_clip))
+        _check_state("theta", tr.theta, o_theta, theta0, errs, bad)
+        _check_state("grad_norm", gnorm, o_gn.detach().reshape(1), None, errs, bad)
+        _check_state("loss", loss.sum().reshape(1), o_loss.reshape(1), None, errs, bad)
+        _check_state("loss_aux", terms.mean(dim=0), torch.stack([o_aux[k] for k in PDE_TERMS[pde]]), None, errs, bad)
+        _check_state("m_theta", tr.m_theta, st["m"].detach(), None, errs, bad)
+        _check_state("v_theta", tr.v_theta, st["v"].detach(), None, errs, bad)
+    assert not bad, f"fine-tune train_step {pde} {L}x{W} (clip {grad_clip}): {bad} (all: {errs})"
+    return errs, clipped

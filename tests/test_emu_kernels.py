@@ -57,3 +57,27 @@ def test_leap_outer(emu_kernels, opt):
 
 def test_leap_outer_clip(emu_kernels):
     pc.check_leap(emu_kernels, "td_burgers", 32, 2, 70, T=2, K_steps=2, inner_lr=1e-3, clip=0.5)
+
+
+# ---- outer train steps vs oracle/meta.py (rows a13, a14-outer, a15, f1): fused clip + Adam(theta) + Adam(alpha) kernel ----
+@pytest.mark.parametrize("grad_clip", [1e14, 1e-3])
+def test_maml_train_step_matches_oracle(emu_kernels, grad_clip):
+    errs, clipped = pc.check_maml_train_steps(emu_kernels, "poisson", 32, 2, 30, T=2, K_steps=2, steps=3, grad_clip=grad_clip)
+    assert all(clipped) == (grad_clip < 1.0) and any(clipped) == (grad_clip < 1.0), clipped
+
+
+def test_maml_train_step_sgd_and_rmsprop(emu_kernels):
+    pc.check_maml_train_steps(emu_kernels, "poisson", 32, 2, 30, T=2, K_steps=2, steps=2, optimizer="sgd")
+    pc.check_maml_train_steps(emu_kernels, "poisson", 32, 2, 30, T=2, K_steps=2, steps=2, optimizer="rmsprop")
+
+
+@pytest.mark.parametrize("grad_clip", [1e14, 1e-3])
+def test_leap_train_step_matches_oracle(emu_kernels, grad_clip):
+    errs, clipped = pc.check_leap_train_steps(emu_kernels, "poisson", 32, 2, 30, T=2, K_steps=2, steps=3, grad_clip=grad_clip)
+    assert all(clipped) == (grad_clip < 1.0), clipped
+
+
+@pytest.mark.parametrize("grad_clip", [1e14, 1e-3])
+def test_finetune_train_step_matches_oracle(emu_kernels, grad_clip):
+    errs, clipped = pc.check_finetune_train_steps(emu_kernels, "td_burgers", 32, 2, 70, T=2, steps=3, grad_clip=grad_clip)
+    assert all(clipped) == (grad_clip < 1.0), clipped

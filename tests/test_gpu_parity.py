@@ -185,3 +185,88 @@ def test_trainer_cuda_graph_matches_eager(gpu_kernels):
             assert tr.graph_launches > 50
     for a, b in zip(res[0], res[1]):
         assert torch.equal(a, b)
+
+
+# ---------------------------------------------------------------------------------------------
+# round 2: the outer train steps against oracle/meta.py (rows a13, a14-outer, a15, f1) and the tensor-core path at
+# rollout level (VERDICT r1 "what's weak" 1-3)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("grad_clip", [1e14, 1e-3])
+def test_maml_train_step_matches_oracle(gpu_kernels, grad_clip):
+    # 3x64 (the published network): theta, alpha tree, Adam moments and meta_grad_norm after each of 3 steps
+    errs, clipped = pc.check_maml_train_steps(gpu_kernels, "poisson", 64, 3, 128, T=3, K_steps=2, steps=3, grad_clip=grad_clip)
+    assert all(clipped) == (grad_clip < 1.0), clipped
+
+
+def test_maml_train_step_tensor_core_and_graph(gpu_kernels):
+    # width 128: tcgen05 kernels inside the trainer; and the CUDA-graph replay route of the 3x64 trainer
+    pc.check_maml_train_steps(gpu_kernels, "poisson", 128, 2, 96, T=2, K_steps=2, steps=2, grad_clip=1e-3)
+    pc.check_maml_train_steps(gpu_kernels, "td_burgers", 64, 3, 126, T=2, K_steps=2, steps=3, use_cuda_graph=True)
+    pc.check_maml_train_steps(gpu_kernels, "poisson", 64, 3, 64, T=2, K_steps=2, steps=2, optimizer="sgd")
+
+
+@pytest.mark.parametrize("pde,W,L,clip", [("poisson", 64, 3, 1e14), ("td_burgers", 64, 3, 1e-3), ("poisson", 128, 2, 1e14)])
+def test_leap_train_step_matches_oracle(gpu_kernels, pde, W, L, clip):
+    pc.check_leap_train_steps(gpu_kernels, pde, W, L, 126, T=2, K_steps=3, steps=3, grad_clip=clip)
+
+
+@pytest.mark.parametrize("pde,W,L,clip", [("poisson", 64, 3, 1e14), ("hyper_elasticity", 64, 3, 1e-3), ("td_burgers", 256, 2, 1e14)])
+def test_finetune_train_step_matches_oracle(gpu_kernels, pde, W, L, clip):
+    pc.check_finetune_train_steps(gpu_kernels, pde, W, L, 126, T=2, steps=3, grad_clip=clip)
+
+
+@pytest.mark.parametrize("pde,lr,clip", [("poisson", 1e-2, 1e-2), ("td_burgers", 1e-2, 1e-2), ("hyper_elasticity", 1e-4, 1e-1)])
+def test_maml_outer_c5_network_k5_clip_active(gpu_kernels, pde, lr, clip):
+    """The bench workload's exact call sequence -- mpde_maml_outer on the 5x256 net, K = 5, inner clip ACTIVE (tc_pde GRAD,
+    tc_wgrad row splits, tc_hvp spills, maml_inner_vjp clip branch) -- against the float64 oracle at a small point count."""
+    errs = pc.check_maml(gpu_kernels, pde, 256, 5, 128, T=2, K_steps=5, inner_lr=lr, clip=clip, decay=0.1)
+    print(pde, errs)
+
+
+@pytest.mark.parametrize("W,L", [(128, 3), (256, 2)])
+def test_leap_outer_tensor_core_path(gpu_kernels, W, L):
+    pc.check_leap(gpu_kernels, "poisson", W, L, 200, T=2, K_steps=3, inner_lr=1e-3, inner_opt="adam")
+    pc.check_leap(gpu_kernels, "td_burgers", W, L, 126, T=2, K_steps=2, inner_lr=1e-2, inner_opt="sgd")
+
+
+def _oracle_grad_hv_chunked(pde, W, L, theta, sets, prm, v, chunk=2048):
+    """float64 loss / grad / H v of ONE task at full point counts, accumulated over chunks of points (the loss is a sum of
+    per-set means, so it is linear in the per-chunk means weighted by chunk size / set size)."""
+    lf = pc.oracle_loss_fn(pde, W, L, 1.0)
+    n_b, n_d = sets[0].shape[1], sets[1].shape[1]
+    th = theta.double().requires_grad_(True)
+    loss = torch.zeros((), dtype=torch.float64)
+    g = torch.zeros_like(th)
+    h = torch.zeros_like(th)
+    from helpers import oracle_params
+    prm_t = oracle_params(pde, prm, 0)
+    for c0 in range(0, max(n_b, n_d), chunk):
+        b = sets[0][0, c0:c0 + chunk].double()
+        d = sets[1][0, c0:c0 + chunk].double()
+        _, aux = lf(th, (b, d), prm_t)
+        l = aux["boundary_loss"] * (b.shape[0] / n_b) + aux["domain_loss"] * (d.shape[0] / n_d)
+        (gc,) = torch.autograd.grad(l, th, create_graph=True)
+        (hc,) = torch.autograd.grad((gc * v.double()).sum(), th)
+        loss += l.detach(); g += gc.detach(); h += hc
+    return loss, g, h
+
+
+@pytest.mark.parametrize("W,L", [(128, 2), (256, 5)])
+def test_full_size_task_against_float64_oracle(gpu_kernels, W, L):
+    """ONE task at C5's full 16384 + 16384 points on the tensor-core path against the float64 oracle (values, not
+    properties): pins the long-row accumulation of tc_wgrad_kernel (fp32 master copy every 128 rows) at 1e-4."""
+    K = gpu_kernels
+    n = 16384
+    theta = synthetic.siren_theta([W] * L, 1, 30.0, 30.0, True, seed=0, bias_scale=0.05)
+    sets, prm = synthetic.make_tasks("poisson", 1, [n, n], seed=1)
+    v = torch.randn(1, theta.numel(), generator=torch.Generator().manual_seed(9))
+    net = K.net_desc(L, W, 1, 30.0, True)
+    dsets = [s.to(K.device) for s in sets]
+    l1, _, g1 = K.loss_grad(net, "poisson", 1.0, theta.to(K.device), dsets, prm.to(K.device), 1)
+    l1, g1 = l1.clone(), g1.clone()
+    l2, _, g2, hv = K.loss_hvp(net, "poisson", 1.0, theta.to(K.device), v.to(K.device), dsets, prm.to(K.device), 1)
+    lo, go, ho = _oracle_grad_hv_chunked("poisson", W, L, theta, sets, prm, v[0])
+    errs = {"loss": abs(float(l1[0]) - float(lo)) / abs(float(lo)), "grad": rel_l2(g1[0].cpu(), go), "grad_hvp_call": rel_l2(g2[0].cpu(), go),
+            "hv": rel_l2(hv[0].cpu(), ho)}
+    print(f"{L}x{W} at 16384+16384 points:", errs)
+    assert all(e < 1e-4 for e in errs.values()), errs
