@@ -58,6 +58,10 @@ TC_DEV void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---- register reallocation between warpgroups (all warps of a warpgroup execute the same one) ----------------
+template <int N> TC_DEV void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> TC_DEV void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // ---- bulk copy global -> shared (1-D, completes on an mbarrier) --------------------------------------
 TC_DEV void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

@@ -19,7 +19,12 @@ namespace tc {
 constexpr int HR = 64;                   // jet rows per HVP tile (MMA N)
 
 template <int W> struct HvGeo {
-  static constexpr int NMT = W / 128, KSL = W / 64, NEPI = W, NT = W + 64;
+  static constexpr int NMT = W / 128, KSL = W / 64, NEPI = W;
+  // W = 256: 8 epilogue warps + one control warpgroup (producer warp, MMA warp, two idle warps).  The control warpgroup
+  // hands its registers to the epilogue warps (setmaxnreg): 12 warps launch at 168 registers, the epilogue then runs at
+  // 232 (no local-memory spills, deeper load batches) and the control warps at 40.
+  static constexpr bool REGSHIFT = (W == 256);
+  static constexpr int NT = REGSHIFT ? W + 128 : W + 64;
   static constexpr int SLAB = HR * 128;                 // [64 rows][64 k] fp16
   static constexpr int XBYTES = 2 * KSL * SLAB;         // hi slabs then lo slabs (one operand)
   static constexpr int RING = NSTAGE * STAGE_BYTES;
@@ -544,6 +549,9 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
   const int nst_fwd = (L - 1) * PER + G::KSL;
   const int nsteps = 2 * L - 1;                              // L-1 hidden, output, L-1 adjoint contractions
 
+  if (G::REGSHIFT) {
+    if (warp < G::NEPI / 32) setmaxnreg_inc<232>(); else setmaxnreg_dec<40>();
+  }
   if (warp < G::NEPI / 32) {
     int seq = 0; uint32_t dpar = 0;
     const int* wshift = p.wshift + (size_t)task * p.wshift_stride;
@@ -588,7 +596,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
         }
       }
     }
-  } else {
+  } else if (warp == G::NEPI / 32 + 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
