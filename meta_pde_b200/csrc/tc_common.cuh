@@ -69,6 +69,10 @@ TC_DEV void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint6
                "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// ask L2 for `bytes` (multiple of 16) of global memory starting at a 16-byte aligned address; no completion
+TC_DEV void bulk_prefetch_l2(const void* src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
 // generic-proxy writes to shared memory -> visible to the async proxy (tcgen05.mma operand reads)
 TC_DEV void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -135,6 +139,23 @@ TC_DEV uint64_t desc_kmajor(uint32_t start) { return smem_desc_sw128(start, 16, 
 // MN-major operand: 128-byte runs along M/N; the next 128 B of M/N are `slab_stride` bytes away (LBO), the next
 // 8 K rows 1024 B away (SBO).  `start` = slab + (k0 / 8) * 1024.
 TC_DEV uint64_t desc_mnmajor(uint32_t start, uint32_t slab_stride) { return smem_desc_sw128(start, slab_stride, 1024); }
+
+// The same descriptors from precomputed halves: the upper word is constant (SBO 1024, version 1, 128-byte swizzle), the lower
+// word is (start >> 4) | (LBO >> 4) << 16, so advancing an operand inside its slab is one 32-bit add on the lower word.
+constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+TC_DEV uint32_t desc_lo_kmajor(uint32_t start) { return (start >> 4) | (1u << 16); }
+TC_DEV uint32_t desc_lo_mnmajor(uint32_t start, uint32_t slab_stride) { return (start >> 4) | ((slab_stride >> 4) << 16); }
+TC_DEV uint64_t desc_join(uint32_t lo) { return ((uint64_t)DESC_HI << 32) | (uint64_t)lo; }
+
+// One lane of a CONVERGED warp (all 32 lanes must execute it).  The MMA issuer loops run warp-uniform and only the
+// tcgen05.mma / tcgen05.commit instructions sit behind this predicate: issued from inside an `if (lane == 0)` region,
+// ptxas cannot prove the descriptors uniform and wraps every UTCHMMA in a vote / elect / branch loop (~10 dependent
+// instructions, ~90 cycles per MMA measured in round 2: slower than the 32-64 cycles an N = 64 / 128 MMA executes).
+TC_DEV bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 
 enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_TF32 = 2 };
 // Instruction descriptor (32 bit): D format F32 [4,6)=1, A format [7,10), B format [10,13), A MN-major bit 15,

@@ -24,7 +24,7 @@ template <int W> struct HvGeo {
   // hands its registers to the epilogue warps (setmaxnreg): 12 warps launch at 168 registers, the epilogue then runs at
   // 232 (no local-memory spills, deeper load batches) and the control warps at 40.
   static constexpr bool REGSHIFT = (W == 256);
-  static constexpr int NT = REGSHIFT ? W + 128 : W + 64;
+  static constexpr int NT = REGSHIFT ? W + 128 : W + 96;   // + producer, MMA issuer and record-prefetch warps
   static constexpr int SLAB = HR * 128;                 // [64 rows][64 k] fp16
   static constexpr int XBYTES = 2 * KSL * SLAB;         // hi slabs then lo slabs (one operand)
   static constexpr int RING = NSTAGE * STAGE_BYTES;
@@ -108,57 +108,77 @@ struct HvTile {
     *reinterpret_cast<uint4*>(xb + o) = hv;
     *reinterpret_cast<uint4*>(xb + LO_OFF + o) = lv;
   }
-  // one point: CP rows of the primal and of the tangent operand
-  static TC_DEV void store_point(uint8_t* xb, uint8_t* xdb, int pl, int n, const float* a, const float* ad, const float (&ys)[8]) {
-    if (VAL) {
-      store_x(xb, pl, n, a[0] * ys[0]);
-      store_x(xdb, pl, n, ad[0] * ys[4]);
-    } else {
-      float y4[4], yd4[4];
-      MPDE_UNROLL
-      for (int c = 0; c < 4; ++c) { y4[c] = c < C ? a[c] * ys[c] : 0.f; yd4[c] = c < C ? ad[c] * ys[4 + c] : 0.f; }
-      store_x4(xb, 4 * pl, n, y4);
-      store_x4(xdb, 4 * pl, n, yd4);
-    }
+  // ---- in-place staging (round 2) ------------------------------------------------------------------------
+  // A neuron's part of an operand is 128 B of hi parts + 128 B of lo parts = 64 fp32: exactly its 64 rows in fp32.  The
+  // epilogue therefore parks the fp32 values of a tile IN the operand rows it owns (rows 8j..8j+3 in the 16-byte chunk j
+  // of the hi part, rows 8j+4..8j+7 in chunk j of the lo part), all threads agree on the EXACT channel maxima, and
+  // each thread converts its own chunks to fp16 hi/lo in place.  One pass over tensor memory (the bound pass of round 1
+  // is gone), one sincos per element, and no re-read of zbar from global memory in the reverse pass.
+  static TC_DEV uint32_t chunk_off(int j, int n) {
+    return (uint32_t)(n >> 3) * 1024u + (uint32_t)(n & 7) * 128u + (((uint32_t)j ^ (uint32_t)(n & 7)) << 4);
   }
-  // bounds of |a_c| and |adot_c| from the pre-activation jets (no sincos)
-  static TC_DEV void bound_update(float om, const float* z, const float* zd, float (&bnd)[8]) {
-    const float o2 = om * om;
-    bnd[4] = fmaxf(bnd[4], om * fabsf(zd[0]));
-    if (!VAL) {
-      const float avd = fabsf(zd[0]);
-      bnd[1] = fmaxf(bnd[1], om * fabsf(z[1]));
-      bnd[2] = fmaxf(bnd[2], om * fabsf(z[2]));
-      bnd[5] = fmaxf(bnd[5], om * fabsf(zd[1]) + o2 * fabsf(z[1]) * avd);
-      bnd[6] = fmaxf(bnd[6], om * fabsf(zd[2]) + o2 * fabsf(z[2]) * avd);
-      if (JT::Q) {
-        float pp = 0.f, ppd = 0.f;
-        if (JT::D0) { pp += z[1] * z[1]; ppd += fabsf(z[1] * zd[1]); }
-        if (JT::D1) { pp += z[2] * z[2]; ppd += fabsf(z[2] * zd[2]); }
-        bnd[3] = fmaxf(bnd[3], om * fabsf(z[3]) + o2 * pp);
-        bnd[7] = fmaxf(bnd[7], om * fabsf(zd[3]) + o2 * fabsf(z[3]) * avd + 2.f * o2 * ppd + o2 * om * pp * avd);
+  // 4 consecutive rows r0..r0+3 (r0 % 4 == 0) of neuron n, fp32
+  static TC_DEV void stage4(uint8_t* xb, int r0, int n, float a, float b, float c, float d) {
+    *reinterpret_cast<float4*>(xb + ((r0 & 4) ? LO_OFF : 0u) + chunk_off(r0 >> 3, n)) = make_float4(a, b, c, d);
+  }
+  // all 64 staged rows of neuron n -> fp16 hi / lo operand, scaled by ys[channel]
+  static TC_DEV void convert_rows(uint8_t* xb, int n, const float* ys) {
+    MPDE_UNROLL
+    for (int j = 0; j < HR / 8; ++j) {
+      const uint32_t o = chunk_off(j, n);
+      const float4 a = *reinterpret_cast<const float4*>(xb + o);
+      const float4 b = *reinterpret_cast<const float4*>(xb + LO_OFF + o);
+      uint4 hv, lv;
+      if (VAL) {
+        split2(a.x * ys[0], a.y * ys[0], hv.x, lv.x); split2(a.z * ys[0], a.w * ys[0], hv.y, lv.y);
+        split2(b.x * ys[0], b.y * ys[0], hv.z, lv.z); split2(b.z * ys[0], b.w * ys[0], hv.w, lv.w);
+      } else {
+        split2(a.x * ys[0], a.y * ys[1], hv.x, lv.x); split2(a.z * ys[2], a.w * ys[3], hv.y, lv.y);
+        split2(b.x * ys[0], b.y * ys[1], hv.z, lv.z); split2(b.z * ys[2], b.w * ys[3], hv.w, lv.w);
       }
+      *reinterpret_cast<uint4*>(xb + o) = hv;
+      *reinterpret_cast<uint4*>(xb + LO_OFF + o) = lv;
     }
   }
-  // fold the 8 bounds, barrier, read the shifts.  FWD: the primal value channel is |sin| <= 1.
+  // fold the channel maxima (mx[0..3] primal, mx[4..7] tangent), barrier among the epilogue warps, read the shifts.
+  // FWD: the primal value channel is sin: |a_0| <= 1, fixed shift 14.
   template <bool FWD>
-  static TC_DEV void agree_shifts(HvCtx<W>& cx, int& seq, const float (&bnd)[8], int (&sh)[8], int tid, int lane) {
+  static TC_DEV void agree_shifts(HvCtx<W>& cx, int& seq, const float (&mx)[8], float (&ys)[8], int (&sh)[8], int tid, int lane) {
     uint32_t* cm = cx.cmax + (seq & 1) * 8;
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) {
       const bool used = VAL ? (c == 4 || (!FWD && c == 0)) : ((c & 3) < C && !(FWD && c == 0));
-      if (used) fold_max(cm + c, bnd[c], lane);
+      if (used) fold_max(cm + c, mx[c], lane);
     }
     epi_sync<G::NEPI>();
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) sh[c] = shift_for_max(__uint_as_float(cm[c]));
     if (FWD) sh[0] = 14;
+    MPDE_UNROLL
+    for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
     if (tid == 0) {
       uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 8;
       MPDE_UNROLL
       for (int c = 0; c < 8; ++c) other[c] = 0u;
     }
     ++seq;
+  }
+  // stage one point (CP = 4) / remember one value row (CP = 1: flushed every 4 points) and track the channel maxima
+  static TC_DEV void stage_point(uint8_t* xb, uint8_t* xdb, int pl, int n, const float* a, const float* ad, float (&mx)[8],
+                                 float (&va)[4], float (&vd)[4]) {
+    if (VAL) {
+      va[pl & 3] = a[0]; vd[pl & 3] = ad[0];
+      mx[0] = fmaxf(mx[0], fabsf(a[0])); mx[4] = fmaxf(mx[4], fabsf(ad[0]));
+      if ((pl & 3) == 3) {
+        stage4(xb, pl - 3, n, va[0], va[1], va[2], va[3]);
+        stage4(xdb, pl - 3, n, vd[0], vd[1], vd[2], vd[3]);
+      }
+    } else {
+      MPDE_UNROLL
+      for (int c = 0; c < C; ++c) { mx[c] = fmaxf(mx[c], fabsf(a[c])); mx[4 + c] = fmaxf(mx[4 + c], fabsf(ad[c])); }
+      stage4(xb, 4 * pl, n, a[0], a[1], a[2], C > 3 ? a[3] : 0.f);
+      stage4(xdb, 4 * pl, n, ad[0], ad[1], ad[2], C > 3 ? ad[3] : 0.f);
+    }
   }
 
   // ---- the epilogue side of one tile (all W epilogue threads) ------------------------------------------
@@ -188,34 +208,34 @@ struct HvTile {
       if (gp < sg.n) { x0 = pts[2 * (size_t)gp]; x1 = pts[2 * (size_t)gp + 1]; }
       xs[i] = x0; xs[HR + i] = x1;
     }
-    // ---- layer 0 ----
+    // ---- layer 0 (in_dim = 2): direct ----
     int sh[8];
+    float ys[8];
     {
       const float w00 = mpde_ldg(th + n), w01 = mpde_ldg(th + W + n), b0 = mpde_ldg(th + 2 * W + n);
       const float d00 = mpde_ldg(thd + n), d01 = mpde_ldg(thd + W + n), db0 = mpde_ldg(thd + 2 * W + n);
       epi_sync<G::NEPI>();                              // xs visible
-      float bnd[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int pl = 0; pl < PTS; ++pl) {
-        const float z[4] = {0.f, w00, w01, 0.f};
-        const float zd[4] = {fmaf(d00, xs[pl], fmaf(d01, xs[HR + pl], db0)), d00, d01, 0.f};
-        bound_update(om, z, zd, bnd);
-      }
-      agree_shifts<true>(cx, seq, bnd, sh, tid, lane);
-      float ys[8];
-      for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
+      float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
       MPDE_NOUNROLL
-      for (int pl = 0; pl < PTS; ++pl) {
-        float z[4], zd[4], a[4], ad[4], sv[5];
-        z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[HR + pl], b0)); z[1] = w00; z[2] = w01; z[3] = 0.f;
-        zd[0] = fmaf(d00, xs[pl], fmaf(d01, xs[HR + pl], db0)); zd[1] = d00; zd[2] = d01; zd[3] = 0.f;
-        jet_act_fwd<JK>(om, z, a, sv);
-        jet_act_tan<JK>(om, sv, zd, ad);
+      for (int pl0 = 0; pl0 < PTS; pl0 += 4) {
         MPDE_UNROLL
-        for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
-        MPDE_UNROLL
-        for (int c = 0; c < C; ++c) recp[(size_t)((NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
-        store_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, ys);
+        for (int q = 0; q < 4; ++q) {
+          const int pl = pl0 + q;
+          float z[4], zd[4], a[4], ad[4], sv[5];
+          z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[HR + pl], b0)); z[1] = w00; z[2] = w01; z[3] = 0.f;
+          zd[0] = fmaf(d00, xs[pl], fmaf(d01, xs[HR + pl], db0)); zd[1] = d00; zd[2] = d01; zd[3] = 0.f;
+          jet_act_fwd<JK>(om, z, a, sv);
+          jet_act_tan<JK>(om, sv, zd, ad);
+          MPDE_UNROLL
+          for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
+          MPDE_UNROLL
+          for (int c = 0; c < C; ++c) recp[(size_t)((NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
+          stage_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, mx, va, vd);
+        }
       }
+      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
+      convert_rows(cx.xbuf, n, ys);
+      convert_rows(cx.xdbuf, n, ys + 4);
     }
     fence_proxy_async_smem();
     tc_fence_before();
@@ -230,29 +250,9 @@ struct HvTile {
         const int sw = wshift[l], swd = wshift_d[l];
         for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
       }
-      mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+      mbar_wait(cx.dfull, dpar); dpar ^= 1u;             // every MMA of this layer has completed: X / Xd may be rewritten
       tc_fence_after();
-      float bnd[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      MPDE_NOUNROLL
-      for (int ch = 0; ch < HR / 16; ++ch) {
-        uint32_t v0[16], v1[16], v2[16];
-        tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
-        tmem_ld_wait();
-        MPDE_UNROLL
-        for (int q = 0; q < PPC; ++q) {
-          float z[4] = {0.f, 0.f, 0.f, 0.f}, zd[4] = {0.f, 0.f, 0.f, 0.f};
-          MPDE_UNROLL
-          for (int c = 0; c < C; ++c) {
-            z[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
-            zd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
-          }
-          zd[0] += biasd;
-          bound_update(om, z, zd, bnd);
-        }
-      }
-      agree_shifts<true>(cx, seq, bnd, sh, tid, lane);   // barrier: all MMAs of this layer completed
-      float ys[8];
-      for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
+      float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
       MPDE_NOUNROLL
       for (int ch = 0; ch < HR / 16; ++ch) {
         uint32_t v0[16], v1[16], v2[16];
@@ -274,41 +274,42 @@ struct HvTile {
           for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f)) * (PTS * W) + (pl) * 128] = sv[f];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
-          store_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, ys);
+          stage_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, mx, va, vd);
         }
       }
+      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
+      convert_rows(cx.xbuf, n, ys);
+      convert_rows(cx.xdbuf, n, ys + 4);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(cx.xready);
     }
 
     // ---- output layer: lanes 0..OUT-1 of the first M tile hold y, ydot ----
-    if (mt == 0) {
-      mbar_wait(&cx.dfull[0], dpar); dpar ^= 1u;
-      tc_fence_after();
-      if (warp == 0) {
-        float zs[4], zs1[4], zs2[4];
-        {
-          const int sw = wshift[L], swd = wshift_d[L];
-          for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
-        }
-        MPDE_NOUNROLL
-        for (int ch = 0; ch < HR / 16; ++ch) {
-          uint32_t v0[16], v1[16], v2[16];
-          tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
-          tmem_ld_wait();
-          if (lane < OUT) {
-            MPDE_UNROLL
-            for (int q = 0; q < 16; ++q) {
-              const int c = VAL ? 0 : (q & 3);
-              cx.ybuf[(ch * 16 + q) * 2 + lane] = __uint_as_float(v0[q]) * zs[c];
-              cx.ydbuf[(ch * 16 + q) * 2 + lane] = fmaf(__uint_as_float(v1[q]), zs1[c], __uint_as_float(v2[q]) * zs2[c]);
-            }
+    mbar_wait(cx.dfull, dpar); dpar ^= 1u;
+    tc_fence_after();
+    if (warp == 0) {
+      float zs[4], zs1[4], zs2[4];
+      {
+        const int sw = wshift[L], swd = wshift_d[L];
+        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
+      }
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < HR / 16; ++ch) {
+        uint32_t v0[16], v1[16], v2[16];
+        tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
+        tmem_ld_wait();
+        if (lane < OUT) {
+          MPDE_UNROLL
+          for (int q = 0; q < 16; ++q) {
+            const int c = VAL ? 0 : (q & 3);
+            cx.ybuf[(ch * 16 + q) * 2 + lane] = __uint_as_float(v0[q]) * zs[c];
+            cx.ydbuf[(ch * 16 + q) * 2 + lane] = fmaf(__uint_as_float(v1[q]), zs1[c], __uint_as_float(v2[q]) * zs2[c]);
           }
         }
       }
-      tc_fence_before();
     }
+    tc_fence_before();
     epi_sync<G::NEPI>();
 
     // ---- head: value, seeds ybar and their tangents ybardot ----
@@ -371,13 +372,19 @@ struct HvTile {
     int shz[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int l = L - 1; l >= 0; --l) {
       float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f}, zs2[4] = {0.f, 0.f, 0.f, 0.f};
+      // the first chunk's record loads are issued before the accumulator wait (they do not depend on it)
+      float svb[PPC][NF + C];
+      MPDE_UNROLL
+      for (int q = 0; q < PPC; ++q)
+        MPDE_UNROLL
+        for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + (q) * 128];
       if (l < L - 1) {
         const int sw = wshift[l + 1], swd = wshift_d[l + 1];
         for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-shz[c] - sw); zs1[c] = pow2i(-shz[4 + c] - sw); zs2[c] = pow2i(-shz[c] - swd); }
-        mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+        mbar_wait(cx.dfull, dpar); dpar ^= 1u;           // all adjoint MMAs that read X / Xd have completed
         tc_fence_after();
       }
-      float bnd[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
       float bsum = 0.f, bsumd = 0.f, g0 = 0.f, g1 = 0.f, h0 = 0.f, h1 = 0.f, gw[OUT], hw[OUT];
       MPDE_UNROLL
       for (int o = 0; o < OUT; ++o) { gw[o] = 0.f; hw[o] = 0.f; }
@@ -386,13 +393,6 @@ struct HvTile {
       MPDE_NOUNROLL
       for (int ch = 0; ch < HR / 16; ++ch) {
         uint32_t v0[16], v1[16], v2[16];
-        // all record loads of the chunk are issued before its first spill store and before the accumulator fetch
-        // (see tc_kernels.cuh: the compiler cannot hoist a load above the previous point's stores)
-        float svb[PPC][NF + C];
-        MPDE_UNROLL
-        for (int q = 0; q < PPC; ++q)
-          MPDE_UNROLL
-          for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + (ch * PPC + q) * 128];
         if (l < L - 1) {
           tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
           tmem_ld_wait();
@@ -422,6 +422,11 @@ struct HvTile {
           for (int f = 0; f < NF; ++f) sv[f] = svb[q][f];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) zd[c] = svb[q][NF + c];
+          // this slot's record of the NEXT chunk: in flight while the chunk is processed
+          if (ch + 1 < HR / 16) {
+            MPDE_UNROLL
+            for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + ((ch + 1) * PPC + q) * 128];
+          }
           jet_act_bwd<JK>(om, sv, ab, zb);
           jet_act_bwd_tan<JK>(om, sv, zd, ab, abd, zbd);
           bsum += zb[0]; bsumd += zbd[0];
@@ -447,14 +452,13 @@ struct HvTile {
               h0 += fmaf(xs[pl], zbd[0], zbd[1]); h1 += fmaf(xs[HR + pl], zbd[0], zbd[2]);
             }
           } else {
+            // fp32 spill for tc_wgrad_kernel (written once, never read back here) + the staged copy for the next contraction
             MPDE_UNROLL
             for (int c = 0; c < CP; ++c) {
-              const float z_ = c < C ? zb[c] : 0.f, zd_ = c < C ? zbd[c] : 0.f;
-              zl[(size_t)(CP * pl + c) * W] = z_;
-              zld[(size_t)(CP * pl + c) * W] = zd_;
-              bnd[c] = fmaxf(bnd[c], fabsf(z_));
-              bnd[4 + c] = fmaxf(bnd[4 + c], fabsf(zd_));
+              zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;
+              zld[(size_t)(CP * pl + c) * W] = c < C ? zbd[c] : 0.f;
             }
+            stage_point(cx.xbuf, cx.xdbuf, pl, n, zb, zbd, mx, va, vd);
           }
         }
       }
@@ -473,36 +477,10 @@ struct HvTile {
         epi_sync<G::NEPI>();                              // xs / ybuf are rewritten by the next tile
         break;
       }
-      agree_shifts<false>(cx, seq, bnd, shz, tid, lane);  // barrier: all adjoint MMAs that read X / Xd completed
-      float ys[8];
-      for (int c = 0; c < 8; ++c) ys[c] = pow2i(shz[c]);
-      // zbar_l / zbardot_l back from the spills (L2): the next batch of 8 rows is in flight while this one is stored
-      float zv[8], zdv[8], zv2[8], zdv2[8];
-      MPDE_UNROLL
-      for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)j * W]; zdv[j] = zld[(size_t)j * W]; }
-      MPDE_NOUNROLL
-      for (int r0 = 0; r0 < HR; r0 += 16) {
-        MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) { zv2[j] = zl[(size_t)(r0 + 8 + j) * W]; zdv2[j] = zld[(size_t)(r0 + 8 + j) * W]; }
-        MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) {
-          const int c = VAL ? 0 : (j & 3);
-          zv[j] *= ys[c]; zdv[j] *= ys[4 + c];
-        }
-        store_x8(cx.xbuf, r0, n, zv);
-        store_x8(cx.xdbuf, r0, n, zdv);
-        if (r0 + 16 < HR) {
-          MPDE_UNROLL
-          for (int j = 0; j < 8; ++j) { zv[j] = zl[(size_t)(r0 + 16 + j) * W]; zdv[j] = zld[(size_t)(r0 + 16 + j) * W]; }
-        }
-        MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) {
-          const int c = VAL ? 0 : (j & 3);
-          zv2[j] *= ys[c]; zdv2[j] *= ys[4 + c];
-        }
-        store_x8(cx.xbuf, r0 + 8, n, zv2);
-        store_x8(cx.xdbuf, r0 + 8, n, zdv2);
-      }
+      float ysz[8];
+      agree_shifts<false>(cx, seq, mx, ysz, shz, tid, lane);
+      convert_rows(cx.xbuf, n, ysz);
+      convert_rows(cx.xdbuf, n, ysz + 4);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(cx.xready);
@@ -530,7 +508,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
     if (smem_u32(tc_smem_raw) & 1023u) { printf("tc_hvp_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     for (int i = 0; i < NSTAGE; ++i) { mbar_init(&cx.full[i], 1); mbar_init(&cx.empty[i], 1); }
     mbar_init(cx.xready, G::NEPI);
-    mbar_init(&cx.dfull[0], 1); mbar_init(&cx.dfull[1], 1);
+    mbar_init(cx.dfull, 1);
     mbar_fence_init();
     for (int i = 0; i < 16; ++i) cx.cmax[i] = 0u;
     for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
@@ -597,47 +575,72 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
       }
     }
   } else if (warp == G::NEPI / 32 + 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
-      constexpr uint32_t idesc2 = make_idesc(FMT_F16, 128, 2 * HR, 0, 1);  // N = 128: rows of X then rows of Xd
-      constexpr uint32_t LO_OFF = (uint32_t)W * 128u;
-      const uint32_t xb = smem_u32(cx.xbuf);              // Xd sits XBYTES behind X
-      uint32_t stage = 0, phase = 0, xpar = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        for (int step = 1; step <= nsteps; ++step) {
-          mbar_wait(cx.xready, xpar); xpar ^= 1u;
-          tc_fence_after();
-          const int nmt = (step != L) ? G::NMT : 1;
-          for (int mt = 0; mt < nmt; ++mt) {
-            const uint32_t d01 = tbase + (uint32_t)mt * 2u * HR, d2 = tbase + G::D2 + (uint32_t)mt * HR;
-            for (int which = 0; which < 2; ++which) {
-              uint32_t acc = 0;
-              for (int s = 0; s < G::KSL; ++s) {
-                mbar_wait(&cx.full[stage], phase);
-                tc_fence_after();
-                const uint32_t a_hi = smem_u32(cx.ring + (size_t)stage * STAGE_BYTES), a_lo = a_hi + 16384u;
-                const uint32_t b_hi = xb + (uint32_t)s * 8192u, b_lo = b_hi + LO_OFF;      // k0 = 64 s: 8 atoms of 8 neurons
+    // ===== MMA issuer: the whole warp runs the loop (warp-uniform), one elected lane issues =====
+    constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 1);       // A (weights) K-major, B (jet rows) MN-major
+    constexpr uint32_t idesc2 = make_idesc(FMT_F16, 128, 2 * HR, 0, 1);  // N = 128: rows of X then rows of Xd
+    constexpr uint32_t LO_OFF = (uint32_t)W * 128u;
+    const uint32_t xb = smem_u32(cx.xbuf);                // Xd sits XBYTES behind X
+    const uint32_t ring0 = smem_u32(cx.ring);
+    // lower descriptor words of the B operand at k = 0: W * [X | Xd] (second 64-row block XBYTES further) and Wdot * X
+    const uint32_t bh2_0 = desc_lo_mnmajor(xb, (uint32_t)G::XBYTES), bl2_0 = desc_lo_mnmajor(xb + LO_OFF, (uint32_t)G::XBYTES);
+    const uint32_t bh_0 = desc_lo_mnmajor(xb, LO_OFF), bl_0 = desc_lo_mnmajor(xb + LO_OFF, LO_OFF);
+    uint32_t stage = 0, phase = 0, xpar = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      for (int step = 1; step <= nsteps; ++step) {
+        mbar_wait(cx.xready, xpar); xpar ^= 1u;
+        tc_fence_after();
+        const int nmt = (step != L) ? G::NMT : 1;
+        for (int mt = 0; mt < nmt; ++mt) {
+          const uint32_t d01 = tbase + (uint32_t)mt * 2u * HR, d2 = tbase + G::D2 + (uint32_t)mt * HR;
+          for (int which = 0; which < 2; ++which) {
+            for (int s = 0; s < G::KSL; ++s) {
+              mbar_wait(&cx.full[stage], phase);
+              tc_fence_after();
+              if (elect_one()) {
+                const uint32_t ah_0 = desc_lo_kmajor(ring0 + stage * (uint32_t)STAGE_BYTES), al_0 = ah_0 + (16384u >> 4);
+                const uint32_t koff = (uint32_t)s * (8192u >> 4);            // k0 = 64 s: 8 atoms of 8 neurons
                 MPDE_UNROLL
                 for (int kk = 0; kk < 4; ++kk) {
-                  const uint64_t ah = desc_kmajor(a_hi + kk * 32), al = desc_kmajor(a_lo + kk * 32);
-                  const uint64_t bh = desc_mnmajor(b_hi + kk * 2048, LO_OFF), bl = desc_mnmajor(b_lo + kk * 2048, LO_OFF);
+                  const uint64_t ah = desc_join(ah_0 + kk * 2), al = desc_join(al_0 + kk * 2);      // 32 bytes of K per MMA
+                  const uint32_t acc = (s | kk) ? 1u : 0u;
                   if (which == 0) {
-                    // W * [primal | tangent]: the second block of 64 rows is Xd, XBYTES behind X (leading byte offset)
-                    const uint64_t bh2 = desc_mnmajor(b_hi + kk * 2048, (uint32_t)G::XBYTES);
-                    const uint64_t bl2 = desc_mnmajor(b_lo + kk * 2048, (uint32_t)G::XBYTES);
+                    const uint64_t bh2 = desc_join(bh2_0 + koff + kk * 128), bl2 = desc_join(bl2_0 + koff + kk * 128);
                     mma_f16_ss(d01, ah, bh2, idesc2, acc); mma_f16_ss(d01, al, bh2, idesc2, 1); mma_f16_ss(d01, ah, bl2, idesc2, 1);
                   } else {
+                    const uint64_t bh = desc_join(bh_0 + koff + kk * 128), bl = desc_join(bl_0 + koff + kk * 128);
                     mma_f16_ss(d2, ah, bh, idesc, acc); mma_f16_ss(d2, al, bh, idesc, 1); mma_f16_ss(d2, ah, bl, idesc, 1);   // Wdot * primal
                   }
-                  acc = 1;
                 }
                 tc_commit(&cx.empty[stage]);
-                if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
               }
+              __syncwarp();
+              if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
             }
-            tc_commit(&cx.dfull[mt]);
           }
+        }
+        if (elect_one()) tc_commit(cx.dfull);            // one completion per contraction step: all M tiles
+        __syncwarp();
+      }
+    }
+  }
+  else if (warp == G::NEPI / 32 + 2) {
+    // ===== record prefetcher: the reverse pass reads the activation records of layer l one full contraction step after
+    // this thread asked L2 for them (they were written ~100 us earlier and the per-SM share of L2 does not hold a
+    // whole tile's spills: without the prefetch every batch of record loads pays an HBM round trip) =====
+    if (lane == 0) {
+      uint32_t xpar = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        int sgi = 0;
+        while (sgi + 1 < kp.n_seg && t >= kp.seg_tile_begin[sgi + 1]) ++sgi;
+        const int tile = t - kp.seg_tile_begin[sgi];
+        const int head = kp.seg[sgi].head;
+        const int jk = (head == HEAD_POISSON_DOMAIN) ? JET_LAP : (head == HEAD_BURGERS_DOMAIN) ? JET_XX : (head == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
+        const size_t per_layer = (size_t)rec_fields_points_hvp(jk) * W;       // floats of one (tile, layer) record block
+        const float* rec_tile = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[sgi] + (size_t)tile * L * per_layer;
+        for (int step = 1; step <= nsteps; ++step) {
+          mbar_wait(cx.xready, xpar); xpar ^= 1u;
+          const int l = 2 * L - 2 - step;                // step L + j (j = 0 .. L-2) -> layer L-2-j
+          if (step >= L && l >= 0) bulk_prefetch_l2(rec_tile + (size_t)l * per_layer, (uint32_t)(per_layer * sizeof(float)));
         }
       }
     }

@@ -33,7 +33,10 @@ template <int W> struct TcGeo {
   static constexpr int NMT = W / 128;                 // M tiles (128 neurons each)
   static constexpr int KSL = W / 64;                  // 64-wide k slabs
   static constexpr int NEPI = W;                      // epilogue threads
-  static constexpr int NT = W + 64;                   // + producer warp + MMA warp
+  // + producer, MMA issuer and record-prefetch warps.  W = 256: a full control warpgroup (one idle warp) that hands its
+  // registers to the 8 epilogue warps (setmaxnreg: 12 warps launch at 168 registers, the epilogue then runs at 232)
+  static constexpr bool REGSHIFT = (W == 256);
+  static constexpr int NT = REGSHIFT ? W + 128 : W + 96;
   static constexpr int SLAB = TR * 128;               // bytes of one [128 rows][64 k] fp16 slab
   static constexpr int XBYTES = 2 * KSL * SLAB;       // hi slabs then lo slabs
   static constexpr int RING = NSTAGE * STAGE_BYTES;
@@ -210,46 +213,69 @@ struct TcTile {
     *reinterpret_cast<uint4*>(xbuf + LO_OFF + o) = lv;
   }
 
-  // upper bounds of |a_c| over this thread's points from the pre-activation jet z (no sincos needed)
-  static TC_DEV void bound_update(float om, const float* z, float (&bnd)[4]) {
-    if (!VAL) {
-      bnd[1] = fmaxf(bnd[1], om * fabsf(z[1]));
-      bnd[2] = fmaxf(bnd[2], om * fabsf(z[2]));
-      if (JT::Q) {
-        float pp = 0.f;
-        if (JT::D0) pp += z[1] * z[1];
-        if (JT::D1) pp += z[2] * z[2];
-        bnd[3] = fmaxf(bnd[3], om * fabsf(z[3]) + om * om * pp);
+  // ---- in-place staging (round 2; see HvTile in tc_hvp.cuh) -------------------------------------------------
+  // Neuron n owns, in each of the two 64-row blocks of the operand, 128 B of hi parts and 128 B of lo parts: 512 B = its
+  // 128 rows in fp32.  The epilogue parks the fp32 values of the tile in those bytes (rows 8j..8j+3 of a block in chunk j of
+  // its hi part, rows 8j+4..8j+7 in chunk j of its lo part), the threads agree on the EXACT channel maxima, and every thread
+  // converts its own chunks to fp16 hi/lo in place: one pass over tensor memory, one sincos per element, and no re-read of
+  // zbar from global memory in the reverse pass.
+  static TC_DEV uint32_t chunk_off(int r0, int n) {      // chunk of rows r0..r0+7 (r0 % 8 == 0) of neuron n, hi part
+    return (uint32_t)(r0 >> 6) * NBLK_BYTES + (uint32_t)(n >> 3) * 1024u + (uint32_t)(n & 7) * 128u +
+           (((((uint32_t)r0 & 63u) >> 3) ^ (uint32_t)(n & 7)) << 4);
+  }
+  static TC_DEV void stage4(uint8_t* xb, int r0, int n, float a, float b, float c, float d) {   // rows r0..r0+3, r0 % 4 == 0
+    *reinterpret_cast<float4*>(xb + ((r0 & 4) ? LO_OFF : 0u) + chunk_off(r0 & ~7, n)) = make_float4(a, b, c, d);
+  }
+  static TC_DEV void convert_rows(uint8_t* xb, int n, const float* ys) {
+    MPDE_UNROLL
+    for (int r0 = 0; r0 < TR; r0 += 8) {
+      const uint32_t o = chunk_off(r0, n);
+      const float4 a = *reinterpret_cast<const float4*>(xb + o);
+      const float4 b = *reinterpret_cast<const float4*>(xb + LO_OFF + o);
+      uint4 hv, lv;
+      if (VAL) {
+        split2(a.x * ys[0], a.y * ys[0], hv.x, lv.x); split2(a.z * ys[0], a.w * ys[0], hv.y, lv.y);
+        split2(b.x * ys[0], b.y * ys[0], hv.z, lv.z); split2(b.z * ys[0], b.w * ys[0], hv.w, lv.w);
+      } else {
+        split2(a.x * ys[0], a.y * ys[1], hv.x, lv.x); split2(a.z * ys[2], a.w * ys[3], hv.y, lv.y);
+        split2(b.x * ys[0], b.y * ys[1], hv.z, lv.z); split2(b.z * ys[2], b.w * ys[3], hv.w, lv.w);
       }
+      *reinterpret_cast<uint4*>(xb + o) = hv;
+      *reinterpret_cast<uint4*>(xb + LO_OFF + o) = lv;
     }
   }
-  // all epilogue threads: fold bounds, barrier, read the shifts of this layer's output; record them in shifts[l]
-  // `seq` counts the calls of this thread (selects the cmax half; the other half is cleared for the next call).
-  template <bool ALL = false>
-  static TC_DEV void agree_shifts(TcCtx<W>& cx, int l, int& seq, const float (&bnd)[4], int (&sh)[4], int tid, int lane) {
+  // fold the channel maxima, barrier among the epilogue warps, read the shifts.  FWD: the value channel is sin, |a_0| <= 1.
+  template <bool FWD>
+  static TC_DEV void agree_shifts(TcCtx<W>& cx, int& seq, const float (&mx)[4], float (&ys)[4], int (&sh)[4], int tid, int lane) {
     uint32_t* cm = cx.cmax + (seq & 1) * 4;
-    if (ALL) fold_max(cm + 0, bnd[0], lane);
-    if (!VAL) {
-      fold_max(cm + 1, bnd[1], lane);
-      fold_max(cm + 2, bnd[2], lane);
-      if (JT::Q) fold_max(cm + 3, bnd[3], lane);
+    MPDE_UNROLL
+    for (int c = 0; c < 4; ++c) {
+      const bool used = VAL ? (!FWD && c == 0) : (c < C && !(FWD && c == 0));
+      if (used) fold_max(cm + c, mx[c], lane);
     }
     epi_sync<G::NEPI>();
-    sh[0] = ALL ? shift_for_max(__uint_as_float(cm[0])) : 14;   // forward value channel: |sin| <= 1
-    sh[1] = sh[2] = sh[3] = 0;
-    if (!VAL) {
-      sh[1] = shift_for_max(__uint_as_float(cm[1]));
-      sh[2] = shift_for_max(__uint_as_float(cm[2]));
-      if (JT::Q) sh[3] = shift_for_max(__uint_as_float(cm[3]));
-    }
+    MPDE_UNROLL
+    for (int c = 0; c < 4; ++c) sh[c] = shift_for_max(__uint_as_float(cm[c]));
+    if (FWD) sh[0] = 14;
+    MPDE_UNROLL
+    for (int c = 0; c < 4; ++c) ys[c] = pow2i(sh[c]);
     if (tid == 0) {
-      if (!ALL) { for (int c = 0; c < 4; ++c) cx.shifts[l * 4 + c] = sh[c]; }
       uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 4;
       other[0] = other[1] = other[2] = other[3] = 0u;
     }
     ++seq;
   }
-
+  static TC_DEV void stage_point(uint8_t* xb, int pl, int n, const float* a, float (&mx)[4], float (&va)[4]) {
+    if (VAL) {
+      va[pl & 3] = a[0];
+      mx[0] = fmaxf(mx[0], fabsf(a[0]));
+      if ((pl & 3) == 3) stage4(xb, pl - 3, n, va[0], va[1], va[2], va[3]);
+    } else {
+      MPDE_UNROLL
+      for (int c = 0; c < C; ++c) mx[c] = fmaxf(mx[c], fabsf(a[c]));
+      stage4(xb, 4 * pl, n, a[0], a[1], a[2], C > 3 ? a[3] : 0.f);
+    }
+  }
 
   // ---- the epilogue side of one tile (all W epilogue threads) ------------------------------------------
   static TC_DEV void run(const TcParams& p, TcCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile,
@@ -267,6 +293,7 @@ struct TcTile {
     const uint32_t tlane = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * TR);
     float* xs = cx.xs;
     constexpr int NF = JT::NF;
+    constexpr int PPC = 32 / CP;                        // points per 32-row chunk
     // activation records of this tile: [layer][field][point][neuron]
     float* recp = nullptr;
     if (MODE != MODE_LOSS)
@@ -282,32 +309,29 @@ struct TcTile {
     }
     // ---- layer 0 (in_dim = 2): direct ----
     int sh[4];
+    float ys[4];
     {
       const float w00 = mpde_ldg(th + n), w01 = mpde_ldg(th + W + n), b0 = mpde_ldg(th + 2 * W + n);
-      float bnd[4] = {0.f, 0.f, 0.f, 0.f};
-      { const float z[4] = {0.f, w00, w01, 0.f}; bound_update(om, z, bnd); }
-      agree_shifts(cx, 0, seq, bnd, sh, tid, lane);     // also orders the xs writes before the reads below
-      float ys[4];
-      for (int c = 0; c < 4; ++c) ys[c] = pow2i(sh[c]);
+      epi_sync<G::NEPI>();                              // xs visible
+      float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
       MPDE_NOUNROLL
-      for (int pl = 0; pl < PTS; ++pl) {
-        float z[4], a[4], sv[5];
-        z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[TR + pl], b0));
-        z[1] = w00; z[2] = w01; z[3] = 0.f;
-        jet_act_fwd<JK>(om, z, a, sv);
-        if (MODE != MODE_LOSS) {
-          MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
-        }
-        if (VAL) {
-          store_x(cx.xbuf, pl, n, a[0] * ys[0]);
-        } else {
-          float y4[4];
-          MPDE_UNROLL
-          for (int c = 0; c < 4; ++c) y4[c] = c < C ? a[c] * ys[c] : 0.f;
-          store_x4(cx.xbuf, 4 * pl, n, y4);
+      for (int pl0 = 0; pl0 < PTS; pl0 += 4) {
+        MPDE_UNROLL
+        for (int q = 0; q < 4; ++q) {
+          const int pl = pl0 + q;
+          float z[4], a[4], sv[5];
+          z[0] = fmaf(w00, xs[pl], fmaf(w01, xs[TR + pl], b0));
+          z[1] = w00; z[2] = w01; z[3] = 0.f;
+          jet_act_fwd<JK>(om, z, a, sv);
+          if (MODE != MODE_LOSS) {
+            MPDE_UNROLL
+            for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
+          }
+          stage_point(cx.xbuf, pl, n, a, mx, va);
         }
       }
+      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
+      convert_rows(cx.xbuf, n, ys);
     }
     fence_proxy_async_smem();
     tc_fence_before();
@@ -318,92 +342,54 @@ struct TcTile {
       const float bias = mpde_ldg(th + ph_off_layer(W, l) + 2 * W * W + n);
       float zs[4];
       { const int sw = wshift[l]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
-      mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+      mbar_wait(cx.dfull, dpar); dpar ^= 1u;             // every MMA of this layer has completed: X may be rewritten
       tc_fence_after();
-      // pass 1: bounds of the output channels
-      float bnd[4] = {0.f, 0.f, 0.f, 0.f};
-      if (!VAL) {
-        MPDE_NOUNROLL
-        for (int ch = 0; ch < TR / 32; ++ch) {
-          uint32_t v[32];
-          tmem_ld32(tlane + ch * 32, v);
-          tmem_ld_wait();
-          MPDE_UNROLL
-          for (int q = 0; q < 8; ++q) {
-            float z[4];
-            MPDE_UNROLL
-            for (int c = 0; c < 4; ++c) z[c] = __uint_as_float(v[4 * q + c]) * zs[c];
-            bound_update(om, z, bnd);
-          }
-        }
-      }
-      agree_shifts(cx, l, seq, bnd, sh, tid, lane);     // barrier: every MMA of this layer has completed
-      float ys[4];
-      for (int c = 0; c < 4; ++c) ys[c] = pow2i(sh[c]);
-      // pass 2
+      float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
       MPDE_NOUNROLL
       for (int ch = 0; ch < TR / 32; ++ch) {
         uint32_t v[32];
         tmem_ld32(tlane + ch * 32, v);
         tmem_ld_wait();
-        if (VAL) {
-          float y8[8];
+        MPDE_UNROLL
+        for (int q = 0; q < PPC; ++q) {
+          const int pl = ch * PPC + q;
+          float z[4] = {0.f, 0.f, 0.f, 0.f}, a[4], sv[5];
           MPDE_UNROLL
-          for (int q = 0; q < 32; ++q) {
-            float z[1], a[1], sv[2];
-            z[0] = fmaf(__uint_as_float(v[q]), zs[0], bias);
-            jet_act_fwd<JK>(om, z, a, sv);
-            if (MODE != MODE_LOSS) {
-              MPDE_UNROLL
-              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (ch * 32 + q) * 128] = sv[f];
-            }
-            y8[q & 7] = a[0] * ys[0];
-            if ((q & 7) == 7) store_x8(cx.xbuf, ch * 32 + q - 7, n, y8);
-          }
-        } else {
-          MPDE_UNROLL
-          for (int q = 0; q < 8; ++q) {
-            float z[4], a[4], sv[5];
+          for (int c = 0; c < C; ++c) z[c] = __uint_as_float(v[CP * q + c]) * zs[c];
+          z[0] += bias;
+          jet_act_fwd<JK>(om, z, a, sv);
+          if (MODE != MODE_LOSS) {
             MPDE_UNROLL
-            for (int c = 0; c < 4; ++c) z[c] = __uint_as_float(v[4 * q + c]) * zs[c];
-            z[0] += bias;
-            jet_act_fwd<JK>(om, z, a, sv);
-            if (MODE != MODE_LOSS) {
-              MPDE_UNROLL
-              for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (ch * 8 + q) * 128] = sv[f];
-            }
-            float y4[4];
-            MPDE_UNROLL
-            for (int c = 0; c < 4; ++c) y4[c] = c < C ? a[c] * ys[c] : 0.f;
-            store_x4(cx.xbuf, ch * 32 + 4 * q, n, y4);
+            for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (pl) * 128] = sv[f];
           }
+          stage_point(cx.xbuf, pl, n, a, mx, va);
         }
       }
+      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
+      convert_rows(cx.xbuf, n, ys);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(cx.xready);
     }
 
     // ---- output layer: D0 lanes 0..OUT-1 hold y[o][row] ----
-    if (mt == 0) {
-      mbar_wait(&cx.dfull[0], dpar); dpar ^= 1u;
-      tc_fence_after();
-      if (warp == 0) {
-        float zs[4];
-        { const int sw = wshift[L]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
-        MPDE_NOUNROLL
-        for (int ch = 0; ch < TR / 32; ++ch) {
-          uint32_t v[32];
-          tmem_ld32(tlane + ch * 32, v);
-          tmem_ld_wait();
-          if (lane < OUT) {
-            MPDE_UNROLL
-            for (int q = 0; q < 32; ++q) cx.ybuf[(ch * 32 + q) * 2 + lane] = __uint_as_float(v[q]) * zs[VAL ? 0 : (q & 3)];
-          }
+    mbar_wait(cx.dfull, dpar); dpar ^= 1u;
+    tc_fence_after();
+    if (warp == 0) {
+      float zs[4];
+      { const int sw = wshift[L]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
+      MPDE_NOUNROLL
+      for (int ch = 0; ch < TR / 32; ++ch) {
+        uint32_t v[32];
+        tmem_ld32(tlane + ch * 32, v);
+        tmem_ld_wait();
+        if (lane < OUT) {
+          MPDE_UNROLL
+          for (int q = 0; q < 32; ++q) cx.ybuf[(ch * 32 + q) * 2 + lane] = __uint_as_float(v[q]) * zs[VAL ? 0 : (q & 3)];
         }
       }
-      tc_fence_before();
     }
+    tc_fence_before();
     epi_sync<G::NEPI>();
 
     // ---- head: one thread per point ----
@@ -456,7 +442,8 @@ struct TcTile {
     // =====================================================================================================
     // reverse pass: thread n owns neuron n of every layer.  abar_l comes from the seeds (l = L-1) or
     // from the adjoint contraction D[k][row] = sum_n W_{l+1}[k][n] zbar_{l+1}[row][n] in TMEM; zbar_l goes (a) in fp32
-    // to the spill read by tc_wgrad_kernel and (b) as fp16 hi/lo into X, the B operand of the next adjoint contraction.
+    // to the spill read by tc_wgrad_kernel and (b) staged in place, then as fp16 hi/lo, into X: the B operand of the
+    // next adjoint contraction.
     // =====================================================================================================
     float* ps = p.psmall + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
     float* zsp_tile = p.zsp + (size_t)task * p.zsp_task_stride +
@@ -470,15 +457,22 @@ struct TcTile {
       ps[ps_off_wl(W, L) + W * OUT + tid] += g;
     }
     int shz[4] = {0, 0, 0, 0};
+    constexpr int SB = VAL ? 16 : 8;                    // points per batch of record loads
     for (int l = L - 1; l >= 0; --l) {
       float zs[4] = {0.f, 0.f, 0.f, 0.f};
+      // the first batch of record loads is issued before the accumulator wait (it does not depend on it)
+      float svb[SB][NF];
+      MPDE_UNROLL
+      for (int qq = 0; qq < SB; ++qq)
+        MPDE_UNROLL
+        for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (qq) * 128];
       if (l < L - 1) {
         const int sw = wshift[l + 1];
         for (int c = 0; c < 4; ++c) zs[c] = pow2i(-shz[c] - sw);
-        mbar_wait(&cx.dfull[mt], dpar); dpar ^= 1u;
+        mbar_wait(cx.dfull, dpar); dpar ^= 1u;           // all adjoint MMAs that read X have completed
         tc_fence_after();
       }
-      float bnd[4] = {0.f, 0.f, 0.f, 0.f};
+      float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
       float bsum = 0.f, g0 = 0.f, g1 = 0.f, gw[OUT];
       MPDE_UNROLL
       for (int o = 0; o < OUT; ++o) gw[o] = 0.f;
@@ -486,19 +480,9 @@ struct TcTile {
       MPDE_NOUNROLL
       for (int ch = 0; ch < TR / 32; ++ch) {
         uint32_t v[32];
-        constexpr int PPC = 32 / CP;                      // points per 32-row chunk
-        constexpr int SB = VAL ? 16 : 8;                  // points per batch of record loads
+        if (l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
         MPDE_UNROLL
         for (int q0 = 0; q0 < PPC; q0 += SB) {
-        // All record loads of the batch are issued before anything is stored (the compiler cannot move a load above
-        // the zbar spill stores of the previous point: one exposed memory latency per point, ncu r01e) and before
-        // the accumulator chunk is fetched from tensor memory.
-        float svb[SB][NF];
-        MPDE_UNROLL
-        for (int qq = 0; qq < SB; ++qq)
-          MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (ch * PPC + q0 + qq) * 128];
-        if (q0 == 0 && l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
         MPDE_UNROLL
         for (int qq = 0; qq < SB; ++qq) {
           const int q = q0 + qq;
@@ -517,6 +501,11 @@ struct TcTile {
           }
           MPDE_UNROLL
           for (int f = 0; f < NF; ++f) sv[f] = svb[qq][f];
+          // this slot's record of the NEXT batch: in flight while the batch is processed
+          if (pl + SB < PTS) {
+            MPDE_UNROLL
+            for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (pl + SB) * 128];
+          }
           jet_act_bwd<JK>(om, sv, ab, zb);
           bsum += zb[0];
           if (l == L - 1) {
@@ -532,11 +521,8 @@ struct TcTile {
             else { g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[TR + pl], zb[0], zb[2]); }
           } else {
             MPDE_UNROLL
-            for (int c = 0; c < CP; ++c) {
-              const float z_ = c < C ? zb[c] : 0.f;
-              zl[(size_t)(CP * pl + c) * W] = z_;
-              bnd[c] = fmaxf(bnd[c], fabsf(z_));
-            }
+            for (int c = 0; c < CP; ++c) zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;   // fp32 spill for tc_wgrad_kernel
+            stage_point(cx.xbuf, pl, n, zb, mx, va);
           }
         }
         }
@@ -548,29 +534,9 @@ struct TcTile {
         for (int o = 0; o < OUT; ++o) ps[ps_off_wl(W, L) + n * OUT + o] += gw[o];
       }
       if (l == 0) { ps[n] += g0; ps[W + n] += g1; epi_sync<G::NEPI>(); break; }   // xs is rewritten by the next tile
-      // zbar_l -> X (B operand of the adjoint contraction with W_l)
-      agree_shifts<true>(cx, l, seq, bnd, shz, tid, lane);      // barrier: all adjoint MMAs that read X have completed
-      float ys[4];
-      for (int c = 0; c < 4; ++c) ys[c] = pow2i(shz[c]);
-      // zbar_l back from the spill (L2), two batches of 8 rows in flight
-      float za[8], zb2[8];
-      MPDE_UNROLL
-      for (int j = 0; j < 8; ++j) za[j] = zl[(size_t)j * W];
-      MPDE_NOUNROLL
-      for (int r0 = 0; r0 < TR; r0 += 16) {
-        MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) zb2[j] = zl[(size_t)(r0 + 8 + j) * W];
-        MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) za[j] *= ys[VAL ? 0 : (j & 3)];
-        store_x8(cx.xbuf, r0, n, za);
-        if (r0 + 16 < TR) {
-          MPDE_UNROLL
-          for (int j = 0; j < 8; ++j) za[j] = zl[(size_t)(r0 + 16 + j) * W];
-        }
-        MPDE_UNROLL
-        for (int j = 0; j < 8; ++j) zb2[j] *= ys[VAL ? 0 : (j & 3)];
-        store_x8(cx.xbuf, r0 + 8, n, zb2);
-      }
+      float ysz[4];
+      agree_shifts<false>(cx, seq, mx, ysz, shz, tid, lane);
+      convert_rows(cx.xbuf, n, ysz);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(cx.xready);
@@ -597,7 +563,7 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
     if (smem_u32(tc_smem_raw) & 1023u) { printf("tc_pde_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     for (int i = 0; i < NSTAGE; ++i) { mbar_init(&cx.full[i], 1); mbar_init(&cx.empty[i], 1); }
     mbar_init(cx.xready, G::NEPI);
-    mbar_init(&cx.dfull[0], 1); mbar_init(&cx.dfull[1], 1);
+    mbar_init(cx.dfull, 1);
     mbar_fence_init();
     for (int i = 0; i < 8; ++i) cx.cmax[i] = 0u;
     for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
@@ -616,6 +582,9 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
   const int nst_tile = nst_fwd + (MODE != MODE_LOSS ? (L - 1) * G::NMT * G::KSL : 0);
   const int nsteps = (MODE != MODE_LOSS) ? 2 * L - 1 : L;    // contractions per tile
 
+  if (G::REGSHIFT && MODE != MODE_LOSS) {
+    if (warp < G::NEPI / 32) setmaxnreg_inc<232>(); else setmaxnreg_dec<40>();
+  }
   if (warp < G::NEPI / 32) {
     // ===== epilogue warps =====
     int seq = 0; uint32_t dpar = 0;
@@ -655,39 +624,62 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
         }
       }
     }
-  } else {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(FMT_F16, 128, TR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
-      constexpr uint32_t NBLK_BYTES = (uint32_t)W * 128u, LO_OFF = (uint32_t)(TR / 64) * NBLK_BYTES;
-      const uint32_t xb = smem_u32(cx.xbuf);
-      uint32_t stage = 0, phase = 0, xpar = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        for (int step = 1; step <= nsteps; ++step) {
-          mbar_wait(cx.xready, xpar); xpar ^= 1u;
-          tc_fence_after();
-          const int nmt = (step != L) ? G::NMT : 1;   // step L is the output layer (one M tile)
-          for (int mt = 0; mt < nmt; ++mt) {
-            const uint32_t d = tbase + (uint32_t)mt * TR;
-            uint32_t acc = 0;
-            for (int s = 0; s < G::KSL; ++s) {
-              mbar_wait(&cx.full[stage], phase);
-              tc_fence_after();
-              const uint32_t a_hi = smem_u32(cx.ring + (size_t)stage * STAGE_BYTES), a_lo = a_hi + 16384u;
-              const uint32_t b_hi = xb + (uint32_t)s * 8192u, b_lo = b_hi + LO_OFF;   // k0 = 64 s: 8 atoms of 8 neurons
+  } else if (warp == G::NEPI / 32 + 1) {
+    // ===== MMA issuer: the whole warp runs the loop (warp-uniform), one elected lane issues (see elect_one) =====
+    constexpr uint32_t idesc = make_idesc(FMT_F16, 128, TR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
+    constexpr uint32_t NBLK_BYTES = (uint32_t)W * 128u, LO_OFF = (uint32_t)(TR / 64) * NBLK_BYTES;
+    const uint32_t xb = smem_u32(cx.xbuf), ring0 = smem_u32(cx.ring);
+    const uint32_t bh_0 = desc_lo_mnmajor(xb, NBLK_BYTES), bl_0 = desc_lo_mnmajor(xb + LO_OFF, NBLK_BYTES);
+    uint32_t stage = 0, phase = 0, xpar = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      for (int step = 1; step <= nsteps; ++step) {
+        mbar_wait(cx.xready, xpar); xpar ^= 1u;
+        tc_fence_after();
+        const int nmt = (step != L) ? G::NMT : 1;   // step L is the output layer (one M tile)
+        for (int mt = 0; mt < nmt; ++mt) {
+          const uint32_t d = tbase + (uint32_t)mt * TR;
+          for (int s = 0; s < G::KSL; ++s) {
+            mbar_wait(&cx.full[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t ah_0 = desc_lo_kmajor(ring0 + stage * (uint32_t)STAGE_BYTES), al_0 = ah_0 + (16384u >> 4);
+              const uint32_t koff = (uint32_t)s * (8192u >> 4);              // k0 = 64 s: 8 atoms of 8 neurons
               MPDE_UNROLL
               for (int kk = 0; kk < 4; ++kk) {
-                const uint64_t ah = desc_kmajor(a_hi + kk * 32), al = desc_kmajor(a_lo + kk * 32);
-                const uint64_t bh = desc_mnmajor(b_hi + kk * 2048, NBLK_BYTES), bl = desc_mnmajor(b_lo + kk * 2048, NBLK_BYTES);
-                mma_f16_ss(d, ah, bh, idesc, acc); acc = 1;
+                const uint64_t ah = desc_join(ah_0 + kk * 2), al = desc_join(al_0 + kk * 2);
+                const uint64_t bh = desc_join(bh_0 + koff + kk * 128), bl = desc_join(bl_0 + koff + kk * 128);
+                mma_f16_ss(d, ah, bh, idesc, (s | kk) ? 1u : 0u);
                 mma_f16_ss(d, al, bh, idesc, 1);
                 mma_f16_ss(d, ah, bl, idesc, 1);
               }
               tc_commit(&cx.empty[stage]);
-              if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
             }
-            tc_commit(&cx.dfull[mt]);
+            __syncwarp();
+            if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
           }
+        }
+        if (elect_one()) tc_commit(cx.dfull);            // one completion per contraction step: all M tiles
+        __syncwarp();
+      }
+    }
+  }
+  else if (MODE != MODE_LOSS && warp == G::NEPI / 32 + 2) {
+    // ===== record prefetcher (see tc_hvp.cuh): asks L2 for the records of layer l one contraction step before the
+    // reverse pass reads them =====
+    if (lane == 0) {
+      uint32_t xpar = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        int sgi = 0;
+        while (sgi + 1 < kp.n_seg && t >= kp.seg_tile_begin[sgi + 1]) ++sgi;
+        const int tile = t - kp.seg_tile_begin[sgi];
+        const int head = kp.seg[sgi].head;
+        const int jk = (head == HEAD_POISSON_DOMAIN) ? JET_LAP : (head == HEAD_BURGERS_DOMAIN) ? JET_XX : (head == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
+        const size_t per_layer = (size_t)rec_fields_points(jk) * W;           // floats of one (tile, layer) record block
+        const float* rec_tile = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[sgi] + (size_t)tile * L * per_layer;
+        for (int step = 1; step <= nsteps; ++step) {
+          mbar_wait(cx.xready, xpar); xpar ^= 1u;
+          const int l = 2 * L - 2 - step;                // step L + j (j = 0 .. L-2) -> layer L-2-j
+          if (step >= L && l >= 0) bulk_prefetch_l2(rec_tile + (size_t)l * per_layer, (uint32_t)(per_layer * sizeof(float)));
         }
       }
     }

@@ -249,29 +249,31 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
     MPDE_UNROLL
     for (int j = 0; j < MC; ++j) out[j] = master[j];   // gout rows are only 4-byte aligned (P is odd-ish)
   } else if (warp == G::NCONV / 32) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(FMT_TF32, 128, W, 0, 0);
-      for (int st = 0; st < nsteps; ++st) {
-        const int slot = st & 1;
-        const int gen = st / WG_GROUP, b = gen & 1;     // accumulator generation and its TMEM buffer
-        const uint32_t d = tbase + (uint32_t)(b * W);
-        uint32_t acc = (st % WG_GROUP) ? 1u : 0u;       // a fresh accumulator per generation
-        if ((st % WG_GROUP) == 0 && gen >= 2) { mbar_wait(&dfree[b], ((gen >> 1) - 1) & 1); tc_fence_after(); }
-        mbar_wait(&op_full[slot], (st >> 1) & 1);
-        tc_fence_after();
-        const uint32_t hs = smem_u32(smem + (size_t)slot * G::SLOT), zs = hs + G::HBYTES;
+    // ===== MMA issuer: warp-uniform loop, one elected lane issues (see elect_one in tc_common.cuh) =====
+    constexpr uint32_t idesc = make_idesc(FMT_TF32, 128, W, 0, 0);
+    const uint32_t smem0 = smem_u32(smem);
+    for (int st = 0; st < nsteps; ++st) {
+      const int slot = st & 1;
+      const int gen = st / WG_GROUP, b = gen & 1;     // accumulator generation and its TMEM buffer
+      const uint32_t d = tbase + (uint32_t)(b * W);
+      const uint32_t acc0 = (st % WG_GROUP) ? 1u : 0u;  // a fresh accumulator per generation
+      if ((st % WG_GROUP) == 0 && gen >= 2) { mbar_wait(&dfree[b], ((gen >> 1) - 1) & 1); tc_fence_after(); }
+      mbar_wait(&op_full[slot], (st >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t hs = desc_lo_kmajor(smem0 + (uint32_t)slot * (uint32_t)G::SLOT), zs = hs + ((uint32_t)G::HBYTES >> 4);
         MPDE_UNROLL
         for (int j = 0; j < WG_QR / 8; ++j) {           // 8 rows of r (32 bytes of K) per MMA; lo parts 64 bytes further
-          const uint64_t ah = desc_kmajor(hs + j * 32), al = desc_kmajor(hs + 64 + j * 32);
-          const uint64_t bh = desc_kmajor(zs + j * 32), bl = desc_kmajor(zs + 64 + j * 32);
-          mma_tf32_ss(d, ah, bh, idesc, acc); acc = 1;
+          const uint64_t ah = desc_join(hs + j * 2), al = desc_join(hs + 4 + j * 2);
+          const uint64_t bh = desc_join(zs + j * 2), bl = desc_join(zs + 4 + j * 2);
+          mma_tf32_ss(d, ah, bh, idesc, j ? 1u : acc0);
           mma_tf32_ss(d, al, bh, idesc, 1);
           mma_tf32_ss(d, ah, bl, idesc, 1);
         }
         tc_commit(&op_empty[slot]);
         if ((st % WG_GROUP) == WG_GROUP - 1 || st == nsteps - 1) tc_commit(&dfull[b]);
       }
+      __syncwarp();
     }
   } else {
     // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lanes 1..: one record field each) =====
