@@ -25,6 +25,29 @@ def sin(x):
     return torch.sin(x)
 
 
+def siren_init(omega):
+    """field.py:23-34: U(-sqrt(6 / fan_in) / omega, +sqrt(6 / fan_in) / omega) (threefry draws of compat.random)."""
+    def init_fn(key, shape, dtype=np.float32, omega=omega):
+        lim = np.sqrt(6.0 / shape[0]) / omega
+        return jrandom.uniform(key, shape, minval=-lim, maxval=lim)
+    return init_fn
+
+
+def first_layer_siren_init(omega, omega0):
+    """field.py:37-44: (omega0 / omega) * U(-1 / fan_in, +1 / fan_in)."""
+    def init_fn(key, shape, dtype=np.float32, omega=omega, omega0=omega0):
+        lim = 1.0 / shape[0]
+        return np.float32(omega0 / omega) * jrandom.uniform(key, shape, minval=-lim, maxval=lim)
+    return init_fn
+
+
+def constant_init(val):
+    """field.py:140-143: val * ones (the log io-scales)."""
+    def initializer(key, shape, dtype=np.float32):
+        return np.full(tuple(shape), val, np.float32)
+    return initializer
+
+
 class FieldSpec:
     """Bound constructor arguments of a field class."""
 
@@ -98,17 +121,12 @@ class _FieldBase(metaclass=_FieldMeta):
         vals = []
         for (path, shp), k in zip(shapes, keys):
             if path[-1] == "kernel":
-                fan_in = shp[0]
-                if path[0] == "Dense_0":
-                    lim = 1.0 / fan_in
-                    v = (spec.omega0 / spec.omega) * jrandom.uniform(k, shp, minval=-lim, maxval=lim)
-                else:
-                    lim = math.sqrt(6.0 / fan_in) / spec.omega
-                    v = jrandom.uniform(k, shp, minval=-lim, maxval=lim)
+                init = first_layer_siren_init(spec.omega, spec.omega0) if path[0] == "Dense_0" else siren_init(spec.omega)
+                v = init(k, shp)
             elif path[-1] == "bias":
                 v = np.zeros(shp, np.float32)
             else:
-                v = np.full(shp, math.log(1.0 / FLAGS.io_scale_lr_factor), np.float32)
+                v = constant_init(math.log(1.0 / FLAGS.io_scale_lr_factor))(k, shp)
             vals.append(np.asarray(v, np.float32).reshape(-1))
         theta = torch.from_numpy(np.concatenate(vals))
         model = Model(cls, theta)

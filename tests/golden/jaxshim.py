@@ -53,6 +53,8 @@ def _patch_tensor():
     torch.Tensor.__getitem__ = _getitem
     torch.Tensor.transpose = _transpose
     torch.Tensor.astype = lambda self, dt: self.to(_dtype(dt))
+    _orig_rsub = torch.Tensor.__rsub__
+    torch.Tensor.__rsub__ = lambda self, o: _orig_rsub(self.to(torch.int64) if self.dtype == torch.bool else self, o)   # numpy's 1 - mask
     torch.Tensor._jaxshim_patched = True
 
 
@@ -267,6 +269,44 @@ def uniform(key, shape=(), dtype=None, minval=0.0, maxval=1.0):
 
 def normal(key, shape=(), dtype=None):
     return torch.as_tensor(_gen(key, 0x53).standard_normal(size=tuple(shape)), dtype=DT)
+
+
+def use_threefry(jr):
+    """Swap the stand-in's hashed PRNG for `jr` (meta_pde_b200.compat.random: the Threefry-2x32 restatement of jax 0.2.20's
+    jax.random) so that the reference's SAMPLER and INIT source can be executed with the key stream the compat layer uses.
+    Keys are int64 tensors holding the two uint32 words (so that the reference's `key * FLAGS.vary_x` works)."""
+    def k_(key):
+        return _onp.asarray([int(v) & 0xFFFFFFFF for v in _t(key).reshape(-1).tolist()], dtype=_onp.uint32)
+
+    def f_(x):
+        return float(x.item()) if torch.is_tensor(x) else float(x)
+
+    def out_key(a):
+        return torch.as_tensor(_onp.asarray(a, dtype=_onp.int64))
+
+    def t_uniform(key, shape=(), dtype=None, minval=0.0, maxval=1.0):
+        return torch.as_tensor(jr.uniform(k_(key), tuple(shape), minval=f_(minval), maxval=f_(maxval)).astype(_onp.float64))
+
+    def t_choice(key, a, shape=(), replace=True, p=None):
+        assert not replace and p is not None and isinstance(a, int)
+        idx = jr.choice_without_replacement(k_(key), int(a), int(shape[0]), _t(p).to(torch.float32).numpy())
+        return torch.as_tensor(_onp.asarray(idx, dtype=_onp.int64))
+
+    rnd = sys.modules["jax.random"]
+    rnd.PRNGKey = lambda seed: out_key(jr.PRNGKey(int(seed)))
+    rnd.split = lambda key, num=2: out_key(jr.split(k_(key), int(num)))
+    rnd.uniform = t_uniform
+    rnd.normal = lambda key, shape=(), dtype=None: torch.as_tensor(jr.normal(k_(key), tuple(shape)).astype(_onp.float64))
+    rnd.choice = t_choice
+    rnd.randint = lambda key, shape, minval, maxval: torch.as_tensor(
+        jr.randint(k_(key), tuple(shape), int(_t(minval).reshape(-1)[0]), int(_t(maxval).reshape(-1)[0])).astype(_onp.int64))
+
+
+def _while_loop(cond, body, init):
+    val = init
+    while bool(cond(val)):
+        val = body(val)
+    return val
 
 
 # ------------------------------------------------------------------------------------------------ flax.nn
@@ -490,8 +530,18 @@ def _make_jnp():
     m.zeros_like = lambda x: torch.zeros_like(_t(x))
     m.identity = lambda n: torch.eye(n, dtype=DT)
     m.eye = m.identity
-    m.linspace = lambda a, b, n: torch.linspace(float(a), float(b), int(n), dtype=DT)
-    m.arange = lambda *a: torch.arange(*a)
+    def _linspace(a, b, n, endpoint=True):
+        a, b, n = float(a), float(b), int(n)
+        return torch.linspace(a, b, n, dtype=DT) if endpoint else torch.linspace(a, b, n + 1, dtype=DT)[:-1]
+    m.linspace = _linspace
+    m.arange = lambda *a, dtype=None: torch.arange(*a)
+    def _repeat(x, n, axis=None):
+        x = _t(x)
+        if x.dim() == 0 or axis is None:
+            return torch.repeat_interleave(x.reshape(-1), int(n))
+        return torch.repeat_interleave(x, int(n), dim=axis)
+    m.repeat = _repeat
+    m.tile = lambda x, reps: _t(x).repeat(*reps)
     m.matmul = lambda a, b: _t(a) @ _t(b)
     m.dot = m.matmul
     m.transpose = lambda x: _t(x).T
@@ -542,7 +592,7 @@ def install():
     tu.tree_flatten, tu.tree_unflatten, tu.tree_leaves, tu.tree_structure = tree_flatten, tree_unflatten, tree_leaves, tree_structure
     jax.tree_util = tu
     lax = types.ModuleType("jax.lax")
-    lax.scan, lax.cond = _scan, _cond
+    lax.scan, lax.cond, lax.while_loop = _scan, _cond, _while_loop
     jax.lax = lax
     rnd = types.ModuleType("jax.random")
     rnd.PRNGKey, rnd.split, rnd.uniform, rnd.normal = PRNGKey, split, uniform, normal
