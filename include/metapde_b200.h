@@ -130,7 +130,7 @@ int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t
  * maml_inner_step after the gradient (src/nets/maml.py:72-96):
  *   g' = grad * (softplus ? softplus(alpha) : alpha)   alpha: [P] lr-tree row shared by tasks, or NULL: scalar alpha_scalar
  *   n  = ||g'||_2 per task; if n > clip: g' *= clip / n;  theta_next = theta - inner_lr * g'  (Momentum beta=0)
- *   gnorm [T] receives n.  theta may alias nothing; theta_task_stride 0 = shared theta. */
+ *   gnorm [T] (required) receives n.  theta may alias nothing; theta_task_stride 0 = shared theta. */
 int mpde_maml_inner_update(int T, int P, const float* theta, int64_t theta_task_stride, const float* grad,
                            const float* alpha, float alpha_scalar, int softplus_lrs, float inner_lr, float clip,
                            float* theta_next, float* gnorm, void* stream);

@@ -5,7 +5,7 @@ import os
 import torch
 from absl import app
 
-from . import checkpoint, field, flags as cflags, leap, random as jr, trainer_util
+from . import checkpoint, deploy, field, flags as cflags, leap, random as jr, trainer_util
 from .flags import FLAGS
 from .optim import Adam
 from .pdes import get_pde
@@ -57,6 +57,11 @@ def main(argv):
     with open(os.path.join(path, "flags_config.txt"), "w") as f:
         f.write(FLAGS.flags_into_string())
     key, leap_def, Field, optimizer = build(pde)
+    ev = deploy.make_leap_eval_fns(pde, leap_def)       # src/leap_pde.py:140-173
+    key, gt_key, gt_points_key = jr.split(key, 3)
+    gt_params = [pde.sample_params(k) for k in jr.split(gt_key, FLAGS.n_eval)]
+    coords = torch.stack([torch.as_tensor(pde.sample_points_in_domain(k, FLAGS.validation_points, p), dtype=torch.float32)
+                          for k, p in zip(jr.split(gt_points_key, FLAGS.n_eval), gt_params)])
     for step in range(FLAGS.outer_steps):
         key, subkey = jr.split(key, 2)
         with trainer_util.Timer() as t:
@@ -65,8 +70,11 @@ def main(argv):
             log("encountered nan at at step {}".format(step))
             break
         if step % FLAGS.log_every == 0:
-            log("step: {}, losses: {}, meta_grad_norm: {}, per train step time: {}".format(
-                step, losses.mean(dim=0).tolist(), float(meta_grad_norm), t.interval))
+            with trainer_util.Timer() as deploy_timer:                                     # leap_pde.py:224-230
+                trainer_util.vmap_validation_rollout(optimizer.target, gt_params, coords, None, ev.partial_make_coef_func)
+            deployment_time = deploy_timer.interval / FLAGS.n_eval
+            log("step: {}, losses: {}, deployment_time: {}, meta_grad_norm: {}, per train step time: {}".format(
+                step, losses.mean(dim=0).tolist(), deployment_time, float(meta_grad_norm), t.interval))
         if FLAGS.viz_every > 0 and step % FLAGS.viz_every == 0:
             checkpoint.save(path, step, optimizer.target)
     return optimizer

@@ -1,12 +1,15 @@
 """``python -m meta_pde_b200.compat.maml_pde`` -- drop-in for ``python -m src.maml_pde`` (src/maml_pde.py) on the
 hot path: same flags, same MamlDef / Field construction, same train_step semantics (src/maml_pde.py:203-226), NaN stop,
-text log and pickle checkpoints.  FEniCS validation and plots are out of scope."""
+text log and pickle checkpoints, and the deployment rollout of the n_eval validation tasks (get_final_model /
+make_coef_func / validation_losses, src/maml_pde.py:163-201) with its ``deployment_time``.  The FEniCS ground truth the
+reference compares those fields with, and the plots, are out of scope: ``val_mse`` etc. are logged
+only when ground-truth values are supplied to ``trainer_util.vmap_validation_error`` by the caller."""
 import os
 
 import torch
 from absl import app
 
-from . import checkpoint, field, flags as cflags, maml, random as jr, trainer_util
+from . import checkpoint, deploy, field, flags as cflags, maml, random as jr, trainer_util
 from .flags import FLAGS
 from .optim import Adam, Momentum
 from .pdes import get_pde
@@ -73,6 +76,13 @@ def main(argv):
     with open(os.path.join(path, "flags_config.txt"), "w") as f:
         f.write(FLAGS.flags_into_string())
     key, maml_def, Field, optimizer, inner_lrs, lr_state = build(pde)
+    ev = deploy.make_maml_eval_fns(pde, maml_def)
+    # validation tasks and their evaluation coordinates (maml_pde.py:228-236; coords come from FEniCS meshes in the
+    # reference, from sample_points_in_domain here)
+    key, gt_key, gt_points_key = jr.split(key, 3)
+    gt_params = [pde.sample_params(k) for k in jr.split(gt_key, FLAGS.n_eval)]
+    coords = torch.stack([torch.as_tensor(pde.sample_points_in_domain(k, FLAGS.validation_points, p), dtype=torch.float32)
+                          for k, p in zip(jr.split(gt_points_key, FLAGS.n_eval), gt_params)])
     log("NN model:", {k: (tuple(v.shape) if torch.is_tensor(v) else {kk: tuple(vv.shape) for kk, vv in v.items()})
                       for k, v in optimizer.target.params.items()})
     for step in range(FLAGS.outer_steps):
@@ -87,8 +97,14 @@ def main(argv):
             log("encountered nan at at step {}".format(step))
             break
         if step % FLAGS.log_every == 0:
-            log("step: {}, meta_loss: {}, losses: {}, meta_grad_norm: {}, per train step time: {}".format(
-                step, float(meta_losses[0].mean()), losses.mean(dim=0).tolist(), float(meta_grad_norm), t.interval))
+            with trainer_util.Timer() as deploy_timer:
+                trainer_util.vmap_validation_rollout((optimizer.target, inner_lrs), gt_params, coords, None,
+                                                     ev.partial_make_coef_func)
+            deployment_time = deploy_timer.interval / FLAGS.n_eval
+            val_losses, val_meta_losses = ev.validation_losses((optimizer.target, inner_lrs))
+            log("step: {}, meta_loss: {}, val_meta_loss: {}, losses: {}, deployment_time: {}, meta_grad_norm: {}, "
+                "time: {}".format(step, float(meta_losses[0].mean()), float(val_meta_losses[0].mean()),
+                                  losses.mean(dim=0).tolist(), deployment_time, float(meta_grad_norm), t.interval))
         if FLAGS.viz_every > 0 and step % FLAGS.viz_every == 0:
             checkpoint.save(path, step, optimizer.target, inner_lrs)
     return optimizer, inner_lrs

@@ -1,5 +1,6 @@
 """The parts of src/util/trainer_util.py the path needs: prepare_logging (text log only: TensorBoard / matplotlib are
-out of scope and absent), get_optimizer; plus src/util/timer.py's Timer with a device synchronise."""
+out of scope and absent), get_optimizer, vmap_validation_error / vmap_validation_rollout (:501-590, ground-truth values
+supplied by the caller: FEniCS is out of scope); plus src/util/timer.py's Timer with a device synchronise."""
 import os
 import shutil
 import time
@@ -7,6 +8,16 @@ import time
 import torch
 
 from .optim import get_optimizer  # noqa: F401
+
+
+def vmap_validation_error(*args, **kwargs):
+    from .deploy import vmap_validation_error as f
+    return f(*args, **kwargs)
+
+
+def vmap_validation_rollout(*args, **kwargs):
+    from .deploy import vmap_validation_rollout as f
+    return f(*args, **kwargs)
 
 
 def prepare_logging(out_dir, expt_name):

@@ -596,7 +596,22 @@ int mpde_maml_inner_update(int T, int P, const float* theta, int64_t theta_task_
   InnerUpdParams p;
   p.P = P; p.theta = theta; p.theta_stride = theta_task_stride; p.grad = grad; p.alpha = alpha; p.alpha_scalar = alpha_scalar;
   p.softplus = softplus_lrs; p.inner_lr = inner_lr; p.clip = clip; p.theta_next = theta_next; p.gnorm = gnorm; p.gnorm_stride = 1;
-  return launch_simple(maml_inner_update_kernel, T, 1, 1024, 1024 * sizeof(float), stream, p);
+  // this entry point has no workspace argument: one chunk per task, the partial is parked in gnorm[t]
+  if (!gnorm) return MPDE_INVALID_ARG;
+  p.part = gnorm;
+  int rc = launch_simple(maml_inner_norm_kernel, 1, T, 1024, 1024 * sizeof(float), stream, p);
+  if (rc) return rc;
+  return launch_simple(maml_inner_update_kernel, 1, T, 1024, 0, stream, p);
+}
+
+// chunks per task of the two-stage inner-step kernels: ~2 CTAs of 256 threads per SM over all tasks, >= 2048 elements each
+static int inner_splits(int T, int P) {
+  long long s = (2LL * device_sm_count() + T - 1) / T;
+  const long long smax = (P + 2047) / 2048;
+  if (s > smax) s = smax;
+  if (s > INNER_MAX_SPLITS) s = INNER_MAX_SPLITS;
+  if (s < 1) s = 1;
+  return (int)s;
 }
 
 size_t mpde_sumsq_workspace_bytes(int64_t n) { (void)n; return 1024 * sizeof(float) + 256; }
@@ -650,7 +665,7 @@ int mpde_outer_step(float* theta, int64_t n_theta, float* lrs, int64_t n_lrs, co
 // ------------------------------------------------------------------ MAML rollout
 struct MamlWs {
   size_t eval_bytes;
-  size_t n_thetas, n_grads, n_lam, n_gbar, n_tmp, n_galpha, n_gnorm, n_M, n_loss1;
+  size_t n_thetas, n_grads, n_lam, n_gbar, n_tmp, n_galpha, n_gnorm, n_M, n_loss1, n_part;
   size_t bytes;
 };
 static int maml_ws(const mpde_net_desc* net, const mpde_pde_desc* pi, const mpde_pde_desc* po, const mpde_maml_cfg* cfg,
@@ -678,9 +693,10 @@ static int maml_ws(const mpde_net_desc* net, const mpde_pde_desc* pi, const mpde
   w->n_gnorm = (size_t)K * T;
   w->n_M = (size_t)K * T;
   w->n_loss1 = (size_t)T;
+  w->n_part = (size_t)T * INNER_MAX_SPLITS;
   Carver c(nullptr, 0);
   c.take(w->n_thetas); c.take(w->n_grads); c.take(w->n_lam); c.take(w->n_gbar); c.take(w->n_tmp); c.take(w->n_galpha);
-  c.take(w->n_gnorm); c.take(w->n_M); c.take(w->n_loss1);
+  c.take(w->n_gnorm); c.take(w->n_M); c.take(w->n_loss1); c.take(w->n_part);
   w->bytes = w->eval_bytes + c.off + 512;
   return MPDE_OK;
 }
@@ -714,7 +730,9 @@ static int maml_impl(const mpde_net_desc* net, const mpde_pde_desc* pi, const mp
   float* thetas = c.take(w.n_thetas); float* grads = c.take(w.n_grads); float* lam = c.take(w.n_lam);
   float* gbar = c.take(w.n_gbar); float* tmp = c.take(w.n_tmp); float* galpha = c.take(w.n_galpha);
   float* gnorm = c.take(w.n_gnorm); float* Mk = c.take(w.n_M); float* loss1 = c.take(w.n_loss1);
+  float* part = c.take(w.n_part);
   (void)loss1;
+  const int S = inner_splits(T, P);
   const int nterms = mpde_num_terms(pi->kind);
 
   // ---- forward sweep: K inner SGD steps (maml.py:132-155) ----
@@ -729,8 +747,10 @@ static int maml_impl(const mpde_net_desc* net, const mpde_pde_desc* pi, const mp
     up.P = P; up.theta = th_k; up.theta_stride = st_k; up.grad = g_k;
     up.alpha = inner_lrs ? inner_lrs + (size_t)k * P : nullptr; up.alpha_scalar = 1.0f; up.softplus = cfg->softplus_lrs;
     up.inner_lr = cfg->inner_lr; up.clip = cfg->inner_grad_clip;
-    up.theta_next = thetas + (size_t)k * TP; up.gnorm = gnorm + (size_t)k * T; up.gnorm_stride = 1;
-    rc = launch_simple(maml_inner_update_kernel, T, 1, 1024, 1024 * sizeof(float), stream, up);
+    up.theta_next = thetas + (size_t)k * TP; up.gnorm = gnorm + (size_t)k * T; up.gnorm_stride = 1; up.part = part;
+    rc = launch_simple(maml_inner_norm_kernel, S, T, 256, 256 * sizeof(float), stream, up);
+    if (rc) return rc;
+    rc = launch_simple(maml_inner_update_kernel, S, T, 256, 0, stream, up);
     if (rc) return rc;
   }
   const float* th_K = thetas + (size_t)(K - 1) * TP;
@@ -765,8 +785,10 @@ static int maml_impl(const mpde_net_desc* net, const mpde_pde_desc* pi, const mp
     vp.P = P; vp.lam = lam; vp.add = tmp; vp.c_add = coef; vp.grad = grads + (size_t)k * TP;
     vp.alpha = inner_lrs ? inner_lrs + (size_t)k * P : nullptr; vp.alpha_scalar = 1.0f; vp.softplus = cfg->softplus_lrs;
     vp.gnorm = gnorm + (size_t)k * T; vp.gnorm_stride = 1; vp.inner_lr = cfg->inner_lr; vp.clip = cfg->inner_grad_clip;
-    vp.gbar = gbar; vp.galpha = (inner_lrs && meta_grad_lrs) ? galpha : nullptr;
-    rc = launch_simple(maml_inner_vjp_kernel, T, 1, 1024, 1024 * sizeof(float), stream, vp);
+    vp.gbar = gbar; vp.galpha = (inner_lrs && meta_grad_lrs) ? galpha : nullptr; vp.part = part;
+    rc = launch_simple(maml_inner_vjp_dot_kernel, S, T, 256, 256 * sizeof(float), stream, vp);
+    if (rc) return rc;
+    rc = launch_simple(maml_inner_vjp_kernel, S, T, 256, 0, stream, vp);
     if (rc) return rc;
     if (vp.galpha) {
       rc = launch_simple(task_sum_kernel, grid_for(P), 1, 256, 0, stream, meta_grad_lrs + (size_t)k * P, (const float*)galpha, T, (long long)P, grad_scale);

@@ -203,6 +203,7 @@ MPDE_GLOBAL void loss_finalize_kernel(LossFinParams p, int T) {
 MPDE_HD float softplus_f(float x) { return (x > 20.f) ? x : log1pf(expf(x)); }
 MPDE_HD float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
 
+constexpr int INNER_MAX_SPLITS = 64;
 struct InnerUpdParams {
   int P;
   const float* theta; long long theta_stride;
@@ -211,31 +212,54 @@ struct InnerUpdParams {
   float inner_lr, clip;
   float* theta_next;                 // [T][P]
   float* gnorm; long long gnorm_stride;
+  float* part;                       // [T][gridDim.x] partial sums of squares (stage 1 -> stage 2)
 };
-// grid T, 1024 threads, smem 1024 floats.  maml.py:72-96
-MPDE_GLOBAL void maml_inner_update_kernel(InnerUpdParams p) {
+// Two stages, grid (S, T) x 256 threads each (round 1 ran one 1024-thread CTA per task: 8 CTAs on 148 SMs at 8 tasks per
+// GPU, the non-scaling tail of the 8-GPU step).  Chunk s of task t = parameters [s * ceil(P / S), ...); the partials are
+// re-added in chunk order by every CTA of stage 2: deterministic, no atomics.   maml.py:72-96
+MPDE_DEV void inner_chunk(int P, int& lo, int& hi) {
+  const int S = gridDim.x, chunk = (P + S - 1) / S;
+  lo = (int)blockIdx.x * chunk;
+  hi = lo + chunk < P ? lo + chunk : P;
+}
+MPDE_DEV float inner_part_total(const float* part, int t) {
+  float tot = 0.f;
+  for (int s = 0; s < (int)gridDim.x; ++s) tot += part[(size_t)t * gridDim.x + s];
+  return tot;
+}
+MPDE_GLOBAL void maml_inner_norm_kernel(InnerUpdParams p) {
   float* sh = reinterpret_cast<float*>(mpde_smem());
-  const int t = blockIdx.x, tid = threadIdx.x, nth = blockDim.x;
-  const float* th = p.theta + (size_t)t * p.theta_stride;
+  const int t = blockIdx.y, tid = threadIdx.x, nth = blockDim.x;
   const float* g = p.grad + (size_t)t * p.P;
-  float* out = p.theta_next + (size_t)t * p.P;
   const float s_scalar = p.softplus ? softplus_f(p.alpha_scalar) : p.alpha_scalar;
+  int lo, hi;
+  inner_chunk(p.P, lo, hi);
   float ss = 0.f;
-  for (int i = tid; i < p.P; i += nth) {
+  for (int i = lo + tid; i < hi; i += nth) {
     const float s = p.alpha ? (p.softplus ? softplus_f(p.alpha[i]) : p.alpha[i]) : s_scalar;
     const float gs = g[i] * s;
     ss = fmaf(gs, gs, ss);
   }
-  const float n = sqrtf(block_sum(ss, sh));
-  const float c = (n > p.clip) ? p.clip / n : 1.f;
-  for (int i = tid; i < p.P; i += nth) {
+  ss = block_sum(ss, sh);
+  if (tid == 0) p.part[(size_t)t * gridDim.x + blockIdx.x] = ss;
+}
+MPDE_GLOBAL void maml_inner_update_kernel(InnerUpdParams p) {
+  const int t = blockIdx.y, tid = threadIdx.x, nth = blockDim.x;
+  const float* th = p.theta + (size_t)t * p.theta_stride;
+  const float* g = p.grad + (size_t)t * p.P;
+  float* out = p.theta_next + (size_t)t * p.P;
+  const float s_scalar = p.softplus ? softplus_f(p.alpha_scalar) : p.alpha_scalar;
+  const float n = sqrtf(inner_part_total(p.part, t));
+  int lo, hi;
+  inner_chunk(p.P, lo, hi);
+  for (int i = lo + tid; i < hi; i += nth) {
     const float s = p.alpha ? (p.softplus ? softplus_f(p.alpha[i]) : p.alpha[i]) : s_scalar;
     float gs = g[i] * s;
     if (n > p.clip) gs = p.clip * gs / n;
-    (void)c;
     out[i] = th[i] - p.inner_lr * gs;
   }
-  if (tid == 0 && p.gnorm) p.gnorm[(size_t)t * p.gnorm_stride] = n;
+  __syncthreads();   // part may alias gnorm (mpde_maml_inner_update: one chunk, partial parked in gnorm[t])
+  if (tid == 0 && blockIdx.x == 0 && p.gnorm) p.gnorm[(size_t)t * p.gnorm_stride] = n;
 }
 
 struct InnerVjpParams {
@@ -248,21 +272,23 @@ struct InnerVjpParams {
   float inner_lr, clip;
   float* gbar;                       // [T][P]: direction for the HVP
   float* galpha;                     // optional [T][P]: per-task lr-tree gradient of this step
+  float* part;                       // [T][gridDim.x] partial dot products (stage 1 -> stage 2)
 };
-// grid T, 1024 threads.  VJP of theta_{k+1} = theta_k - eta * clip(softplus(alpha) * g_k)  
-MPDE_GLOBAL void maml_inner_vjp_kernel(InnerVjpParams p) {
+// VJP of theta_{k+1} = theta_k - eta * clip(softplus(alpha) * g_k)  (SURVEY.md 9.4), two stages, grid (S, T) x 256 threads:
+// stage 1 folds `add` into lam and, for clipped tasks, leaves the chunk's part of <g * s, -eta * lam>; stage 2 finishes.
+MPDE_GLOBAL void maml_inner_vjp_dot_kernel(InnerVjpParams p) {
   float* sh = reinterpret_cast<float*>(mpde_smem());
-  const int t = blockIdx.x, tid = threadIdx.x, nth = blockDim.x;
+  const int t = blockIdx.y, tid = threadIdx.x, nth = blockDim.x;
   float* lam = p.lam + (size_t)t * p.P;
   const float* add = p.add ? p.add + (size_t)t * p.P : nullptr;
   const float* g = p.grad + (size_t)t * p.P;
-  float* gbar = p.gbar + (size_t)t * p.P;
-  float* ga = p.galpha ? p.galpha + (size_t)t * p.P : nullptr;
   const float n = p.gnorm[(size_t)t * p.gnorm_stride];
   const bool clipped = n > p.clip;
   const float s_scalar = p.softplus ? softplus_f(p.alpha_scalar) : p.alpha_scalar;
+  int lo, hi;
+  inner_chunk(p.P, lo, hi);
   float dot = 0.f;
-  for (int i = tid; i < p.P; i += nth) {
+  for (int i = lo + tid; i < hi; i += nth) {
     float l = lam[i];
     if (add) { l = fmaf(p.c_add, add[i], l); lam[i] = l; }
     if (clipped) {
@@ -270,10 +296,23 @@ MPDE_GLOBAL void maml_inner_vjp_kernel(InnerVjpParams p) {
       dot = fmaf(g[i] * s, -p.inner_lr * l, dot);
     }
   }
-  if (clipped) dot = block_sum(dot, sh);
+  dot = block_sum(dot, sh);
+  if (tid == 0) p.part[(size_t)t * gridDim.x + blockIdx.x] = dot;
+}
+MPDE_GLOBAL void maml_inner_vjp_kernel(InnerVjpParams p) {
+  const int t = blockIdx.y, tid = threadIdx.x, nth = blockDim.x;
+  const float* lam = p.lam + (size_t)t * p.P;
+  const float* g = p.grad + (size_t)t * p.P;
+  float* gbar = p.gbar + (size_t)t * p.P;
+  float* ga = p.galpha ? p.galpha + (size_t)t * p.P : nullptr;
+  const float n = p.gnorm[(size_t)t * p.gnorm_stride];
+  const bool clipped = n > p.clip;
+  const float dot = clipped ? inner_part_total(p.part, t) : 0.f;
   const float cn = clipped ? p.clip / n : 1.f;
   const float dn = clipped ? dot / (n * n) : 0.f;
-  for (int i = tid; i < p.P; i += nth) {
+  int lo, hi;
+  inner_chunk(p.P, lo, hi);
+  for (int i = lo + tid; i < hi; i += nth) {
     const float a = p.alpha ? p.alpha[i] : p.alpha_scalar;
     const float s = p.softplus ? softplus_f(a) : a;
     const float ds = p.softplus ? sigmoid_f(a) : 1.f;

@@ -135,3 +135,76 @@ def test_drivers_run_with_reference_flag_strings(gpu_kernels, tmp_path):
                                        f"--load_model_from_expt={tmp_path / 'maml' / 't'}"], tmp_path / "nn")
     assert torch.isfinite(opt3.target.theta).all()
     assert "step: 8" in open(tmp_path / "nn" / "t" / "log.txt").read()
+
+
+@pytest.mark.parametrize("name", ["poisson", "td_burgers"])
+def test_deployment_rollout_matches_oracle(gpu_kernels, flags_small, name):
+    """get_final_model / make_coef_func / vmap_validation_error (src/maml_pde.py:163-201, trainer_util.py:501-575):
+    the batched route (one mpde_maml_adapt + one mpde_field_eval for all n_eval tasks) and the per-task route against
+    the float64 oracle rollout on the same sampled points, same learned lr tree."""
+    from helpers import oracle_points, oracle_params
+    from meta_pde_b200.compat import deploy
+    from oracle.meta import MamlCfg, MamlTask, NetCfg, make_loss_fn, maml_single_task_rollout
+    from oracle.field import make_field_fn, unflatten_params
+
+    saved = {k: FLAGS[k].value for k in ("n_eval", "pde", "num_tsteps", "inner_lr")}
+    try:
+        FLAGS.n_eval, FLAGS.pde, FLAGS.num_tsteps = 3, name, 4
+        if name == "td_burgers":
+            FLAGS.inner_points = 126
+        pde = pdes.get_pde(name)
+        W, L, Ksteps = 64, 3, 3
+        model = _model(pde, W, L)
+        P = model.theta.numel()
+        lrs = field.Model(model.module, 1.0 + 0.2 * torch.randn(Ksteps + 1, P, device="cuda"))
+        mdef = maml.MamlDef(Momentum(learning_rate=1e-2, beta=0.0).create, tasks.make_task_loss_fns_factory(pde), Ksteps,
+                            FLAGS.n_eval, True, 0.1)
+        ev = deploy.make_maml_eval_fns(pde, mdef)
+        gt_params = [pde.sample_params(k) for k in jr.split(jr.PRNGKey(11), FLAGS.n_eval)]
+        coords = torch.stack([torch.as_tensor(pde.sample_points_in_domain(k, 64, p), dtype=torch.float32)
+                              for k, p in zip(jr.split(jr.PRNGKey(12), FLAGS.n_eval), gt_params)])
+        n_c = coords.shape[1]
+        keys = jr.split(jr.PRNGKey(0), FLAGS.n_eval)          # trainer_util.py:505-506
+        # ---- oracle: same key derivations, float64 rollout, plain forward ----
+        net = NetCfg([W] * L, FLAGS.siren_omega, True, 1)
+        lf = make_loss_fn(name, net, float(FLAGS.bc_weight))
+        cfg = MamlCfg(Ksteps, 1e-2, float(FLAGS.inner_grad_clip), True, 0.1)
+        want = []
+        for i in range(FLAGS.n_eval):
+            k1, _ = jr.split(keys[i], 2)
+            pts = pde.sample_points(k1, FLAGS.inner_points, gt_params[i])
+            sets = [torch.as_tensor(s, dtype=torch.float32).cpu().reshape(1, -1, 2) for s in pde.abi_sets(pts)]
+            prm = pde.abi_params(gt_params[i]).cpu().reshape(1, -1)
+            op, opr = oracle_points(name, sets, 0), oracle_params(name, prm, 0)
+            task = MamlTask(opr, [op] * Ksteps, None, op, None)
+            thK, _, _ = maml_single_task_rollout(cfg, lf, model.theta.double().cpu().requires_grad_(True), task, lrs.theta[:Ksteps].double().cpu(),
+                                                 with_outer=False, create_graph=False)
+            f = make_field_fn(unflatten_params(thK.detach(), [W] * L, 2, 1, True), 1, FLAGS.siren_omega)
+            want.append(f(coords[i].double().cpu()).reshape(-1))
+        want = torch.stack(want)
+        # ---- batched route (what vmap_validation_error uses) and per-task route ----
+        got_b = ev.make_coef_funcs(keys, (model, lrs), gt_params, coords).reshape(FLAGS.n_eval, n_c).cpu()
+        got_s = torch.stack([ev.partial_make_coef_func(keys[i], (model, lrs), gt_params[i], coords[i].cuda()).reshape(-1)
+                             for i in range(FLAGS.n_eval)]).cpu()
+        assert rel_l2(got_b, want) < 1e-4 and rel_l2(got_s, want) < 1e-4, (rel_l2(got_b, want), rel_l2(got_s, want))
+        # the adaptation moved the field (otherwise the comparison would be vacuous)
+        base = model(coords[0].cuda()).reshape(-1).cpu()
+        assert rel_l2(got_b[0], base) > 1e-5
+        # ---- error arithmetic against a numpy restatement with synthetic ground truth ----
+        import numpy as np
+        gt_vals = (want + 0.1 * torch.randn_like(want)).numpy()
+        mse, norms, rel, per_dim, rel_std, t_rel = deploy.vmap_validation_error((model, lrs), gt_params, coords, gt_vals,
+                                                                                 ev.partial_make_coef_func)
+        c = want.numpy().reshape(FLAGS.n_eval, n_c, 1); g = gt_vals.reshape(c.shape)
+        err = c - g
+        normalizer = (g ** 2).mean(axis=1, keepdims=True)
+        rsq = err ** 2 / normalizer.mean(axis=2, keepdims=True)
+        assert abs(float(mse) - (err ** 2).mean()) < 1e-4 * (err ** 2).mean()
+        assert abs(float(rel) - rsq.mean()) < 1e-3 * rsq.mean()
+        assert abs(float(rel_std) - rsq.mean(axis=(1, 2)).std()) < 1e-3 * max(rsq.mean(axis=(1, 2)).std(), 1e-12)
+        assert (t_rel is not None) == (name == "td_burgers")
+        if t_rel is not None:
+            assert t_rel.shape == (FLAGS.num_tsteps,) and torch.isfinite(t_rel).all()
+    finally:
+        for k, v in saved.items():
+            setattr(FLAGS, k, v)
