@@ -227,9 +227,9 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
         off += (long long)(pl->tile_begin[s + 1] - pl->tile_begin[s]) * pl->L * rfp * pl->W;
       }
       pl->rec_per_task = off;
-      pl->zsp_per_task = (long long)tiles * (pl->L - 1) * (mode == MODE_HVP ? 64 : 128) * pl->W;
+      pl->zsp_per_task = (long long)tiles * (pl->L - 1) * 64 * pl->W;   // tiles of 64 jet rows in both modes
       pl->PS = tc::ps_count(pl->W, pl->L, pl->OUT);
-      pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS;
+      pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS * (mode == MODE_GRAD ? 2 : 1);   // GRAD: one partial per (CTA, epilogue group)
       {
         // tc_wgrad_kernel: one CTA per (task, layer, k tile) and row split; splits chosen to fill whole waves of the
         // SMs (512 items at T = 64: 3.46 waves -> 2 splits = 6.92; 64 items at T = 8: 0.43 -> 2 splits)
@@ -394,7 +394,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     // hidden kernels: contraction over the task's rows from the spills; small parameters: fixed-order sum over CTAs
     tc::TcWgradParams wp;
     wp.W = pl.W; wp.L = pl.L; wp.T = T; wp.n_seg = pl.n_seg; wp.omega = net->omega;
-    wp.tile_rows = (mode == MODE_HVP) ? 64 : 128; wp.hvp_records = (mode == MODE_HVP); wp.want_hv = 0; wp.zspd = zspd;
+    wp.tile_rows = 64; wp.hvp_records = (mode == MODE_HVP); wp.want_hv = 0; wp.zspd = zspd;
     for (int s = 0; s <= pl.n_seg; ++s) wp.seg_tile_begin[s] = pl.tile_begin[s];
     for (int s = 0; s < pl.n_seg; ++s) {
       wp.seg_jk[s] = (pl.head[s] == HEAD_POISSON_DOMAIN) ? JET_LAP : (pl.head[s] == HEAD_BURGERS_DOMAIN) ? JET_XX
@@ -410,7 +410,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
       if (wprof) cudaEventRecord(ws, (cudaStream_t)stream);
       if (rc) return rc;
     }
-    rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall, gout, pl.P, stream);
+    rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G * (mode == MODE_GRAD ? 2 : 1), T, psmall, gout, pl.P, stream);
     if (rc) return rc;
     if (mode == MODE_HVP) {
       wp.want_hv = 1; wp.gout = hv;

@@ -10,7 +10,7 @@
 //
 // Orientation ("transposed"): D[neuron][row] = sum_k Wt[neuron][k] * X[row][k].  The weights are the A operand
 // (M = 128 neurons per MMA, streamed from L2 through a bulk-copy ring, pre-swizzled by tc_prep_kernel), the tile's
-// jet rows are the MN-major B operand (N = 128 rows resident in shared memory), and a TMEM lane is a neuron: the epilogue
+// jet rows are the MN-major B operand (N = 64 rows per tile, two tiles resident in shared memory), and a TMEM lane is a neuron: the epilogue
 // thread of neuron n reads its accumulator row with tcgen05.ld and has all jet channels of every point of the tile
 // in registers, so the sin-jet algebra is thread-local exactly as in the FP32-FMA kernel.
 //
@@ -25,26 +25,31 @@
 namespace mpde {
 namespace tc {
 
-constexpr int TR = 128;                 // jet rows per tile (MMA N)
+constexpr int TR = 64;                  // jet rows per tile (MMA N)
+constexpr int NSLOT = 2;                // tiles in flight per CTA, one epilogue warp group each (see tc_pde_kernel)
 constexpr int STAGE_BYTES = 32768;      // one ring stage: [128 neurons][64 k] fp16 hi (16 KB) then lo (16 KB)
 constexpr int NSTAGE = 3;
 
 template <int W> struct TcGeo {
   static constexpr int NMT = W / 128;                 // M tiles (128 neurons each)
   static constexpr int KSL = W / 64;                  // 64-wide k slabs
-  static constexpr int NEPI = W;                      // epilogue threads
-  // + producer, MMA issuer and record-prefetch warps.  W = 256: a full control warpgroup (one idle warp) that hands its
-  // registers to the 8 epilogue warps (setmaxnreg: 12 warps launch at 168 registers, the epilogue then runs at 232)
+  static constexpr int NEPI = W;                      // epilogue threads PER SLOT (thread = neuron); NSLOT groups of them
+  // + one control warpgroup: producer, MMA issuer, record prefetcher, one idle warp.  W = 256: 16 epilogue warps + 4 control
+  // warps launch at 96 registers; the control warpgroup then drops to 32 and the epilogue warps rise to 112 (setmaxnreg)
   static constexpr bool REGSHIFT = (W == 256);
-  static constexpr int NT = REGSHIFT ? W + 128 : W + 96;
-  static constexpr int SLAB = TR * 128;               // bytes of one [128 rows][64 k] fp16 slab
-  static constexpr int XBYTES = 2 * KSL * SLAB;       // hi slabs then lo slabs
+  // the pool of setmaxnreg is what the CTA was launched with: 128 control threads x (96 - 32) = 512 epilogue threads x (112 - 96)
+  static constexpr int EPI_REGS = 112, CTL_REGS = 32;
+  static constexpr int NT = NSLOT * W + 128;
+  static constexpr int SLAB = TR * 128;               // bytes of one [64 rows][64 k] fp16 slab
+  static constexpr int XBYTES = 2 * KSL * SLAB;       // one slot's operand: hi slabs then lo slabs
   static constexpr int RING = NSTAGE * STAGE_BYTES;
-  // misc (bytes): xs[2][TR] f32, ybuf[TR][2] f32, red[TR] f32, cmax[2][4] u32, shifts[TC_MAX_L][4] i32, terms[4] f32,
-  //               barriers (2*NSTAGE + 3) u64, tmem slot u32
-  static constexpr int MISC = 2 * TR * 4 + 2 * TR * 4 + TR * 4 + 32 + TC_MAX_L * 16 + 16 + (2 * NSTAGE + 3) * 8 + 16;
-  static constexpr int SMEM = XBYTES + RING + MISC;
-  static constexpr int TMEM_COLS = NMT * TR;          // 128 or 256 (power of two)
+  // per slot (bytes): xs[2][TR] f32, ybuf[TR][2] f32, red[TR] f32, cmax[2][4] u32
+  static constexpr int SLOT_MISC = 2 * TR * 4 + 2 * TR * 4 + TR * 4 + 32;
+  // shared: terms[NSLOT][4] f32, barriers (2*NSTAGE + 2*NSLOT) u64, tmem slot u32
+  static constexpr int MISC = NSLOT * SLOT_MISC + NSLOT * 16 + (2 * NSTAGE + 2 * NSLOT) * 8 + 16;
+  static constexpr int SMEM = NSLOT * XBYTES + RING + MISC;
+  static constexpr int SLOT_COLS = NMT * TR;          // TMEM columns of one slot's accumulators
+  static constexpr int TMEM_COLS = NSLOT * SLOT_COLS; // 128 or 256 (power of two)
   // global weight image per task: hidden layers 1..L-1 (forward copy: NMT*KSL stages each), then the output layer
   static constexpr size_t layer_bytes() { return (size_t)NMT * KSL * STAGE_BYTES; }
   static constexpr size_t out_bytes() { return (size_t)KSL * STAGE_BYTES; }
@@ -125,26 +130,29 @@ extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
 
 template <int W> struct TcCtx {
   typedef TcGeo<W> G;
-  uint8_t* xbuf; uint8_t* ring;
-  float* xs; float* ybuf; float* red; uint32_t* cmax; int* shifts; float* terms;
-  uint64_t* full; uint64_t* empty; uint64_t* xready; uint64_t* dfull;
+  uint8_t* xbuf0; uint8_t* ring; uint8_t* misc0;
+  float* terms;
+  uint64_t* full; uint64_t* empty; uint64_t* xready; uint64_t* dfull;     // xready[NSLOT], dfull[NSLOT]
   uint32_t* tmem_slot;
   TC_DEV void carve() {
     uint8_t* s = tc_smem_raw;
-    xbuf = s; ring = s + G::XBYTES;
-    xs = reinterpret_cast<float*>(ring + G::RING);
-    ybuf = xs + 2 * TR; red = ybuf + 2 * TR;
-    cmax = reinterpret_cast<uint32_t*>(red + TR);
-    shifts = reinterpret_cast<int*>(cmax + 8);
-    terms = reinterpret_cast<float*>(shifts + TC_MAX_L * 4);
-    full = reinterpret_cast<uint64_t*>(terms + 4);
-    empty = full + NSTAGE; xready = empty + NSTAGE; dfull = xready + 1;
-    tmem_slot = reinterpret_cast<uint32_t*>(dfull + 2);
+    xbuf0 = s; ring = s + NSLOT * G::XBYTES;
+    misc0 = ring + G::RING;
+    terms = reinterpret_cast<float*>(misc0 + NSLOT * G::SLOT_MISC);
+    full = reinterpret_cast<uint64_t*>(terms + 4 * NSLOT);
+    empty = full + NSTAGE; xready = empty + NSTAGE; dfull = xready + NSLOT;
+    tmem_slot = reinterpret_cast<uint32_t*>(dfull + NSLOT);
   }
+  // per-slot pieces (slot is a runtime value: plain address arithmetic, no indexed register arrays)
+  TC_DEV uint8_t* xbuf(int slot) const { return xbuf0 + (size_t)slot * G::XBYTES; }
+  TC_DEV float* xs(int slot) const { return reinterpret_cast<float*>(misc0 + (size_t)slot * G::SLOT_MISC); }
+  TC_DEV float* ybuf(int slot) const { return xs(slot) + 2 * TR; }
+  TC_DEV float* red(int slot) const { return xs(slot) + 4 * TR; }
+  TC_DEV uint32_t* cmax(int slot) const { return reinterpret_cast<uint32_t*>(xs(slot) + 5 * TR); }
 };
 
-// barrier among the epilogue warps only (named barrier 1)
-template <int NEPI> TC_DEV void epi_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NEPI) : "memory"); }
+// barrier among the epilogue warps of one group (named barrier 1 + group)
+template <int NEPI> TC_DEV void epi_sync(int grp = 0) { asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(NEPI) : "memory"); }
 
 // warp max of non-negative floats (uint order == float order), folded into shared cmax[c]
 TC_DEV void fold_max(uint32_t* slot, float v, int lane) {
@@ -245,31 +253,38 @@ struct TcTile {
     }
   }
   // fold the channel maxima, barrier among the epilogue warps, read the shifts.  FWD: the value channel is sin, |a_0| <= 1.
+  // `cmx` = this slot's cmax[2][4]; the buffer of agreement seq - 1 stays intact until the barrier of agreement seq, so the
+  // next phase of the slot re-derives the shifts from it (prev_shifts) instead of carrying them in registers.
   template <bool FWD>
-  static TC_DEV void agree_shifts(TcCtx<W>& cx, int& seq, const float (&mx)[4], float (&ys)[4], int (&sh)[4], int tid, int lane) {
-    uint32_t* cm = cx.cmax + (seq & 1) * 4;
+  static TC_DEV void agree_shifts(uint32_t* cmx, int slot, int& seq, const float (&mx)[4], float (&ys)[4], int tid, int lane) {
+    uint32_t* cm = cmx + (seq & 1) * 4;
     MPDE_UNROLL
     for (int c = 0; c < 4; ++c) {
       const bool used = VAL ? (!FWD && c == 0) : (c < C && !(FWD && c == 0));
       if (used) fold_max(cm + c, mx[c], lane);
     }
-    epi_sync<G::NEPI>();
+    epi_sync<G::NEPI>(slot);
     MPDE_UNROLL
-    for (int c = 0; c < 4; ++c) sh[c] = shift_for_max(__uint_as_float(cm[c]));
-    if (FWD) sh[0] = 14;
-    MPDE_UNROLL
-    for (int c = 0; c < 4; ++c) ys[c] = pow2i(sh[c]);
+    for (int c = 0; c < 4; ++c) ys[c] = pow2i((FWD && c == 0) ? 14 : shift_for_max(__uint_as_float(cm[c])));
     if (tid == 0) {
-      uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 4;
+      uint32_t* other = cmx + ((seq & 1) ^ 1) * 4;
       other[0] = other[1] = other[2] = other[3] = 0u;
     }
     ++seq;
   }
-  static TC_DEV void stage_point(uint8_t* xb, int pl, int n, const float* a, float (&mx)[4], float (&va)[4]) {
+  template <bool FWD>
+  static TC_DEV void prev_shifts(const uint32_t* cmx, int seq, int (&sh)[4]) {
+    const uint32_t* cm = cmx + ((seq - 1) & 1) * 4;
+    MPDE_UNROLL
+    for (int c = 0; c < 4; ++c) sh[c] = (FWD && c == 0) ? 14 : shift_for_max(__uint_as_float(cm[c]));
+  }
+  // `qs`: the point's index inside its unrolled group (a compile-time value at every call site; pl % 4 == qs % 4), so that
+  // va[] stays in registers
+  static TC_DEV void stage_point(uint8_t* xb, int pl, int qs, int n, const float* a, float (&mx)[4], float (&va)[4]) {
     if (VAL) {
-      va[pl & 3] = a[0];
+      va[qs & 3] = a[0];
       mx[0] = fmaxf(mx[0], fabsf(a[0]));
-      if ((pl & 3) == 3) stage4(xb, pl - 3, n, va[0], va[1], va[2], va[3]);
+      if ((qs & 3) == 3) stage4(xb, pl - 3, n, va[0], va[1], va[2], va[3]);
     } else {
       MPDE_UNROLL
       for (int c = 0; c < C; ++c) mx[c] = fmaxf(mx[c], fabsf(a[c]));
@@ -277,11 +292,18 @@ struct TcTile {
     }
   }
 
-  // ---- the epilogue side of one tile (all W epilogue threads) ------------------------------------------
-  static TC_DEV void run(const TcParams& p, TcCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile,
-                         uint32_t tbase, int& seq, uint32_t& dpar, const int* wshift) {
+  // ---- one PHASE of one tile (all W epilogue threads) ---------------------------------------------------
+  // A tile advances in phases; between two phases of a tile the tensor core runs the tile's next contraction while the
+  // epilogue warps work on the OTHER slot's tile (tc_pde_kernel).  Phases of a tile (L layers):
+  //   0          points, layer 0 (direct), X_1                                   -> xready
+  //   l = 1..L-1 accumulators of hidden layer l -> activation jets -> X_{l+1}     -> xready
+  //   L          output layer -> head (loss terms, seeds); GRAD: reverse layer L-1 (seeds, no contraction) -> X -> xready
+  //   L + j      GRAD: adjoint accumulators -> reverse layer L-1-j (j = 1..L-1) -> X -> xready (except layer 0)
+  // Nothing but `seq` / `dpar` (parities of the slot's barriers) is carried in registers between the phases of a tile.
+  static TC_DEV void phase(const TcParams& p, TcCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile, int slot,
+                           int ph, uint32_t tbase, int& seq, uint32_t& dpar, const int* wshift) {
     const KParams& kp = p.k;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = (int)threadIdx.x - slot * G::NEPI, lane = tid & 31, warp = tid >> 5;   // indices inside the slot's group
     const int n = tid;                          // this thread's neuron
     const int mt = n >> 7;
     const float om = kp.omega;
@@ -290,29 +312,38 @@ struct TcTile {
     const float* prm = kp.prm + (size_t)task * kp.nprm;
     const int pt0 = tile * PTS;
     const float* pts = sg.pts + (size_t)task * sg.task_stride;
-    const uint32_t tlane = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * TR);
-    float* xs = cx.xs;
+    // a warp may only touch the TMEM lane quarter of its hardware warp id % 4; groups start at multiples of 4 warps
+    const uint32_t tlane = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)mt * (NSLOT * TR) + (uint32_t)slot * TR);
+    float* xs = cx.xs(slot);
+    float* ybuf = cx.ybuf(slot);
+    float* red = cx.red(slot);
+    uint8_t* xbuf = cx.xbuf(slot);
+    uint32_t* cmx = cx.cmax(slot);
+    uint64_t* xready = cx.xready + slot;
+    uint64_t* dfull = cx.dfull + slot;
     constexpr int NF = JT::NF;
-    constexpr int PPC = 32 / CP;                        // points per 32-row chunk
+    // accumulators are read in chunks of TCH columns (rows): 16 keeps the hidden-layer and reverse loops under the 112
+    // registers the 16 epilogue warps of W = 256 run at (32-column chunks + 8-point record batches spilled ~700 bytes)
+    constexpr int TCH = 16;
+    constexpr int PPC = TCH / CP;                       // points per chunk
     // activation records of this tile: [layer][field][point][neuron]
     float* recp = nullptr;
     if (MODE != MODE_LOSS)
       recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NF * PTS) * W +
              (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
 
-    // ---- points ----
-    for (int i = tid; i < PTS; i += G::NEPI) {
-      const int gp = pt0 + i;
-      float x0 = 0.f, x1 = 0.f;
-      if (gp < sg.n) { x0 = pts[2 * (size_t)gp]; x1 = pts[2 * (size_t)gp + 1]; }
-      xs[i] = x0; xs[TR + i] = x1;
-    }
-    // ---- layer 0 (in_dim = 2): direct ----
-    int sh[4];
-    float ys[4];
-    {
+    if (ph == 0) {
+      // ---- points ----
+      for (int i = tid; i < PTS; i += G::NEPI) {
+        const int gp = pt0 + i;
+        float x0 = 0.f, x1 = 0.f;
+        if (gp < sg.n) { x0 = pts[2 * (size_t)gp]; x1 = pts[2 * (size_t)gp + 1]; }
+        xs[i] = x0; xs[TR + i] = x1;
+      }
+      // ---- layer 0 (in_dim = 2): direct ----
+      float ys[4];
       const float w00 = mpde_ldg(th + n), w01 = mpde_ldg(th + W + n), b0 = mpde_ldg(th + 2 * W + n);
-      epi_sync<G::NEPI>();                              // xs visible
+      epi_sync<G::NEPI>(slot);                              // xs visible
       float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
       MPDE_NOUNROLL
       for (int pl0 = 0; pl0 < PTS; pl0 += 4) {
@@ -327,28 +358,32 @@ struct TcTile {
             MPDE_UNROLL
             for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
           }
-          stage_point(cx.xbuf, pl, n, a, mx, va);
+          stage_point(xbuf, pl, q, n, a, mx, va);
         }
       }
-      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
-      convert_rows(cx.xbuf, n, ys);
+      agree_shifts<true>(cmx, slot, seq, mx, ys, tid, lane);
+      convert_rows(xbuf, n, ys);
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(xready);
+      return;
     }
-    fence_proxy_async_smem();
-    tc_fence_before();
-    mbar_arrive(cx.xready);
 
-    // ---- hidden layers 1..L-1: accumulators from TMEM -> activation -> X (in place) ----
-    for (int l = 1; l < L; ++l) {
+    if (ph < L) {
+      // ---- hidden layer l = ph: accumulators from TMEM -> activation -> X (in place) ----
+      const int l = ph;
+      int sh[4];
+      prev_shifts<true>(cmx, seq, sh);
       const float bias = mpde_ldg(th + ph_off_layer(W, l) + 2 * W * W + n);
-      float zs[4];
+      float zs[4], ys[4];
       { const int sw = wshift[l]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
-      mbar_wait(cx.dfull, dpar); dpar ^= 1u;             // every MMA of this layer has completed: X may be rewritten
+      mbar_wait(dfull, dpar); dpar ^= 1u;               // every MMA of this layer has completed: X may be rewritten
       tc_fence_after();
       float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
       MPDE_NOUNROLL
-      for (int ch = 0; ch < TR / 32; ++ch) {
-        uint32_t v[32];
-        tmem_ld32(tlane + ch * 32, v);
+      for (int ch = 0; ch < TR / TCH; ++ch) {
+        uint32_t v[TCH];
+        tmem_ld16(tlane + ch * TCH, v);
         tmem_ld_wait();
         MPDE_UNROLL
         for (int q = 0; q < PPC; ++q) {
@@ -362,103 +397,113 @@ struct TcTile {
             MPDE_UNROLL
             for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (pl) * 128] = sv[f];
           }
-          stage_point(cx.xbuf, pl, n, a, mx, va);
+          stage_point(xbuf, pl, q, n, a, mx, va);
         }
       }
-      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
-      convert_rows(cx.xbuf, n, ys);
+      agree_shifts<true>(cmx, slot, seq, mx, ys, tid, lane);
+      convert_rows(xbuf, n, ys);
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(cx.xready);
+      mbar_arrive(xready);
+      return;
     }
 
-    // ---- output layer: D0 lanes 0..OUT-1 hold y[o][row] ----
-    mbar_wait(cx.dfull, dpar); dpar ^= 1u;
-    tc_fence_after();
-    if (warp == 0) {
-      float zs[4];
-      { const int sw = wshift[L]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
-      MPDE_NOUNROLL
-      for (int ch = 0; ch < TR / 32; ++ch) {
-        uint32_t v[32];
-        tmem_ld32(tlane + ch * 32, v);
-        tmem_ld_wait();
-        if (lane < OUT) {
-          MPDE_UNROLL
-          for (int q = 0; q < 32; ++q) cx.ybuf[(ch * 32 + q) * 2 + lane] = __uint_as_float(v[q]) * zs[VAL ? 0 : (q & 3)];
+    if (ph == L) {
+      // ---- output layer: D0 lanes 0..OUT-1 hold y[o][row] ----
+      int sh[4];
+      prev_shifts<true>(cmx, seq, sh);
+      mbar_wait(dfull, dpar); dpar ^= 1u;
+      tc_fence_after();
+      if (warp == 0) {
+        float zs[4];
+        { const int sw = wshift[L]; for (int c = 0; c < 4; ++c) zs[c] = pow2i(-sh[c] - sw); }
+        MPDE_NOUNROLL
+        for (int ch = 0; ch < TR / TCH; ++ch) {
+          uint32_t v[TCH];
+          tmem_ld16(tlane + ch * TCH, v);
+          tmem_ld_wait();
+          if (lane < OUT) {
+            MPDE_UNROLL
+            for (int q = 0; q < TCH; ++q) ybuf[(ch * TCH + q) * 2 + lane] = __uint_as_float(v[q]) * zs[VAL ? 0 : (q & 3)];
+          }
         }
       }
-    }
-    tc_fence_before();
-    epi_sync<G::NEPI>();
+      tc_fence_before();
+      epi_sync<G::NEPI>(slot);
 
-    // ---- head: one thread per point ----
-    if (tid < PTS) {
-      const int pl = tid;
-      const float* bL = th + ph_off_out(W, L) + W * OUT;
-      float u[OUT * C], ub[OUT * C];
-      MPDE_UNROLL
-      for (int o = 0; o < OUT; ++o)
-        MPDE_UNROLL
-        for (int c = 0; c < C; ++c) {
-          float y = cx.ybuf[(CP * pl + c) * 2 + o];
-          if (c == 0) y += mpde_ldg(bL + o);
-          u[o * C + c] = y;
-        }
-      const int gp = pt0 + pl;
-      const bool valid = gp < sg.n;
-      float res = 0.f;
-      float val = head_eval<HEAD>(u, xs[pl], xs[TR + pl], prm, sg.coef, ub, &res);
-      if (!valid) val = 0.f;
-      cx.red[pl] = val;
-      if (MODE != MODE_LOSS) {
-        // ybuf now carries the seeds ybar[row][o] of the reverse pass (zero for padding points / channels)
+      // ---- head: one thread per point ----
+      if (tid < PTS) {
+        const int pl = tid;
+        const float* bL = th + ph_off_out(W, L) + W * OUT;
+        float u[OUT * C], ub[OUT * C];
         MPDE_UNROLL
         for (int o = 0; o < OUT; ++o)
           MPDE_UNROLL
-          for (int c = 0; c < CP; ++c) cx.ybuf[(CP * pl + c) * 2 + o] = (valid && c < C) ? ub[o * C + c] : 0.f;
-      }
-      if (MODE == MODE_LOSS && valid && sg.res_out != nullptr) {
-        float* ro = sg.res_out + (size_t)task * sg.res_stride;
-        if (HEAD == HEAD_EVAL || HEAD == HEAD_EVAL2) {
+          for (int c = 0; c < C; ++c) {
+            float y = ybuf[(CP * pl + c) * 2 + o];
+            if (c == 0) y += mpde_ldg(bL + o);
+            u[o * C + c] = y;
+          }
+        const int gp = pt0 + pl;
+        const bool valid = gp < sg.n;
+        float res = 0.f;
+        float val = head_eval<HEAD>(u, xs[pl], xs[TR + pl], prm, sg.coef, ub, &res);
+        if (!valid) val = 0.f;
+        red[pl] = val;
+        if (MODE != MODE_LOSS) {
+          // ybuf now carries the seeds ybar[row][o] of the reverse pass (zero for padding points / channels)
           MPDE_UNROLL
-          for (int o = 0; o < OUT; ++o) ro[(size_t)gp * OUT + o] = u[o * C];
-        } else {
-          ro[gp] = res;
+          for (int o = 0; o < OUT; ++o)
+            MPDE_UNROLL
+            for (int c = 0; c < CP; ++c) ybuf[(CP * pl + c) * 2 + o] = (valid && c < C) ? ub[o * C + c] : 0.f;
+        }
+        if (MODE == MODE_LOSS && valid && sg.res_out != nullptr) {
+          float* ro = sg.res_out + (size_t)task * sg.res_stride;
+          if (HEAD == HEAD_EVAL || HEAD == HEAD_EVAL2) {
+            MPDE_UNROLL
+            for (int o = 0; o < OUT; ++o) ro[(size_t)gp * OUT + o] = u[o * C];
+          } else {
+            ro[gp] = res;
+          }
         }
       }
+      epi_sync<G::NEPI>(slot);
+      if (warp == 0) {
+        float s = 0.f;
+        MPDE_UNROLL
+        for (int j = 0; j < (PTS + 31) / 32; ++j) s += (lane + 32 * j < PTS) ? red[lane + 32 * j] : 0.f;
+        MPDE_UNROLL
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) cx.terms[slot * 4 + seg_id] += s;
+      }
+      if (MODE == MODE_LOSS) { epi_sync<G::NEPI>(slot); return; }   // xs / ybuf / red are rewritten by the slot's next tile
     }
-    epi_sync<G::NEPI>();
-    if (warp == 0) {
-      float s = 0.f;
-      MPDE_UNROLL
-      for (int j = 0; j < PTS / 32; ++j) s += cx.red[lane + 32 * j];
-      MPDE_UNROLL
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (lane == 0) cx.terms[seg_id] += s;
-    }
-    if (MODE == MODE_LOSS) return;
 
     // =====================================================================================================
     // reverse pass: thread n owns neuron n of every layer.  abar_l comes from the seeds (l = L-1) or
     // from the adjoint contraction D[k][row] = sum_n W_{l+1}[k][n] zbar_{l+1}[row][n] in TMEM; zbar_l goes (a) in fp32
     // to the spill read by tc_wgrad_kernel and (b) staged in place, then as fp16 hi/lo, into X: the B operand of the
-    // next adjoint contraction.
+    // next adjoint contraction.  One layer per phase: l = L-1 in phase L (right after the head), l = 2L-1-ph after it.
     // =====================================================================================================
-    float* ps = p.psmall + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
+    if (MODE == MODE_LOSS) return;
+    const int l = 2 * L - 1 - ph;
+    float* ps = p.psmall + (((size_t)task * gridDim.x + blockIdx.x) * NSLOT + slot) * p.PS;   // per (CTA, slot) partial
     float* zsp_tile = p.zsp + (size_t)task * p.zsp_task_stride +
                       (size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) * TR * W + n;
     float wl[OUT];
     MPDE_UNROLL
-    for (int o = 0; o < OUT; ++o) wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
-    if (tid < OUT) {   // output bias: sum of the value-channel seeds
-      float g = 0.f;
-      for (int pl = 0; pl < PTS; ++pl) g += cx.ybuf[(CP * pl) * 2 + tid];
-      ps[ps_off_wl(W, L) + W * OUT + tid] += g;
+    for (int o = 0; o < OUT; ++o) wl[o] = 0.f;
+    if (l == L - 1) {
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o) wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
+      if (tid < OUT) {   // output bias: sum of the value-channel seeds
+        float g = 0.f;
+        for (int pl = 0; pl < PTS; ++pl) g += ybuf[(CP * pl) * 2 + tid];
+        ps[ps_off_wl(W, L) + W * OUT + tid] += g;
+      }
     }
-    int shz[4] = {0, 0, 0, 0};
-    constexpr int SB = VAL ? 16 : 8;                    // points per batch of record loads
-    for (int l = L - 1; l >= 0; --l) {
+    constexpr int SB = PPC;                             // points per batch of record loads (one chunk)
+    {
       float zs[4] = {0.f, 0.f, 0.f, 0.f};
       // the first batch of record loads is issued before the accumulator wait (it does not depend on it)
       float svb[SB][NF];
@@ -467,9 +512,11 @@ struct TcTile {
         MPDE_UNROLL
         for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (qq) * 128];
       if (l < L - 1) {
+        int shz[4];
+        prev_shifts<false>(cmx, seq, shz);
         const int sw = wshift[l + 1];
         for (int c = 0; c < 4; ++c) zs[c] = pow2i(-shz[c] - sw);
-        mbar_wait(cx.dfull, dpar); dpar ^= 1u;           // all adjoint MMAs that read X have completed
+        mbar_wait(dfull, dpar); dpar ^= 1u;             // all adjoint MMAs that read X have completed
         tc_fence_after();
       }
       float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
@@ -478,9 +525,9 @@ struct TcTile {
       for (int o = 0; o < OUT; ++o) gw[o] = 0.f;
       float* zl = zsp_tile + (size_t)(l - 1) * TR * W;     // only dereferenced for l >= 1
       MPDE_NOUNROLL
-      for (int ch = 0; ch < TR / 32; ++ch) {
-        uint32_t v[32];
-        if (l < L - 1) { tmem_ld32(tlane + ch * 32, v); tmem_ld_wait(); }
+      for (int ch = 0; ch < TR / TCH; ++ch) {
+        uint32_t v[TCH];
+        if (l < L - 1) { tmem_ld16(tlane + ch * TCH, v); tmem_ld_wait(); }
         MPDE_UNROLL
         for (int q0 = 0; q0 < PPC; q0 += SB) {
         MPDE_UNROLL
@@ -495,7 +542,7 @@ struct TcTile {
             } else {
               float a_ = 0.f;
               MPDE_UNROLL
-              for (int o = 0; o < OUT; ++o) a_ = fmaf(wl[o], cx.ybuf[(CP * pl + c) * 2 + o], a_);
+              for (int o = 0; o < OUT; ++o) a_ = fmaf(wl[o], ybuf[(CP * pl + c) * 2 + o], a_);
               ab[c] = a_;
             }
           }
@@ -514,7 +561,7 @@ struct TcTile {
             MPDE_UNROLL
             for (int o = 0; o < OUT; ++o)
               MPDE_UNROLL
-              for (int c = 0; c < C; ++c) gw[o] = fmaf(a[c], cx.ybuf[(CP * pl + c) * 2 + o], gw[o]);
+              for (int c = 0; c < C; ++c) gw[o] = fmaf(a[c], ybuf[(CP * pl + c) * 2 + o], gw[o]);
           }
           if (l == 0) {
             if (VAL) { g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[TR + pl], zb[0], g1); }
@@ -522,7 +569,7 @@ struct TcTile {
           } else {
             MPDE_UNROLL
             for (int c = 0; c < CP; ++c) zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;   // fp32 spill for tc_wgrad_kernel
-            stage_point(cx.xbuf, pl, n, zb, mx, va);
+            stage_point(xbuf, pl, q, n, zb, mx, va);
           }
         }
         }
@@ -533,20 +580,33 @@ struct TcTile {
         MPDE_UNROLL
         for (int o = 0; o < OUT; ++o) ps[ps_off_wl(W, L) + n * OUT + o] += gw[o];
       }
-      if (l == 0) { ps[n] += g0; ps[W + n] += g1; epi_sync<G::NEPI>(); break; }   // xs is rewritten by the next tile
+      if (l == 0) { ps[n] += g0; ps[W + n] += g1; epi_sync<G::NEPI>(slot); return; }   // xs is rewritten by the slot's next tile
       float ysz[4];
-      agree_shifts<false>(cx, seq, mx, ysz, shz, tid, lane);
-      convert_rows(cx.xbuf, n, ysz);
+      agree_shifts<false>(cmx, slot, seq, mx, ysz, tid, lane);
+      convert_rows(xbuf, n, ysz);
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(cx.xready);
+      mbar_arrive(xready);
     }
   }
 };
 
 // ---------------------------------------------------------------------------------------------------------
-// kernel: grid = (ctas_per_task, T); each CTA walks the task's tiles with stride gridDim.x
+// kernel: grid = (ctas_per_task, T); each CTA walks the task's tiles with stride gridDim.x, TWO tiles at a time
+// (slots 0 / 1: tiles t0 and t0 + gridDim.x).  Round 1 ran one 128-row tile strictly serially (contraction, then
+// epilogue, then contraction ...: tensor pipe 19-30 % active, the epilogue warps parked on the accumulator barrier for a
+// third of the time, and each epilogue warp issuing one instruction every ~5 cycles: a dependent chain, 2 warps per
+// scheduler).  Now each slot has its OWN group of W epilogue threads (thread = neuron), operand buffer, accumulator
+// columns and xready / dfull barriers: twice the warps hide the chains' latency, and the MMA warp runs one slot's
+// contraction while the other group is in its epilogue.  The weight ring is shared (the producer streams each
+// contraction's stages once per slot, in the fixed order slot 0, slot 1 the MMA warp consumes them in).
 // ---------------------------------------------------------------------------------------------------------
+template <int W> TC_DEV int tc_step_first_stage(int step, int L) {
+  constexpr int PER = TcGeo<W>::NMT * TcGeo<W>::KSL;
+  // hidden layer `step` (1..L-1), output layer (step L), adjoint copies of layers L-1..1 (steps L+1..2L-1)
+  return step < L ? (step - 1) * PER : (step == L ? (L - 1) * PER : (L - 1) * PER + TcGeo<W>::KSL + (step - L - 1) * PER);
+}
+
 template <int W, int PDE, int MODE>
 __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_constant__ TcParams p) {
   typedef TcGeo<W> G;
@@ -562,82 +622,99 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
   if (tid == 0) {
     if (smem_u32(tc_smem_raw) & 1023u) { printf("tc_pde_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     for (int i = 0; i < NSTAGE; ++i) { mbar_init(&cx.full[i], 1); mbar_init(&cx.empty[i], 1); }
-    mbar_init(cx.xready, G::NEPI);
-    mbar_init(cx.dfull, 1);
+    for (int i = 0; i < NSLOT; ++i) { mbar_init(&cx.xready[i], G::NEPI); mbar_init(&cx.dfull[i], 1); }
     mbar_fence_init();
-    for (int i = 0; i < 8; ++i) cx.cmax[i] = 0u;
-    for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
+    for (int sl = 0; sl < NSLOT; ++sl)
+      for (int i = 0; i < 8; ++i) cx.cmax(sl)[i] = 0u;
+    for (int i = 0; i < NSLOT * 4; ++i) cx.terms[i] = 0.f;
   }
   if (warp == 0) tmem_alloc(cx.tmem_slot, G::TMEM_COLS);
   if (MODE != MODE_LOSS) {
-    float* ps = p.psmall + (size_t)cta * p.PS;
-    for (int i = tid; i < p.PS; i += G::NT) ps[i] = 0.f;
+    float* ps = p.psmall + (size_t)cta * NSLOT * p.PS;
+    for (int i = tid; i < NSLOT * p.PS; i += G::NT) ps[i] = 0.f;
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = *cx.tmem_slot;
-  // weight-image stages per tile: forward hidden layers + output layer (+ the adjoint copies, layers L-1..1)
-  const int nst_fwd = (L - 1) * G::NMT * G::KSL + G::KSL;
-  const int nst_tile = nst_fwd + (MODE != MODE_LOSS ? (L - 1) * G::NMT * G::KSL : 0);
   const int nsteps = (MODE != MODE_LOSS) ? 2 * L - 1 : L;    // contractions per tile
+  const int nph = (MODE != MODE_LOSS) ? 2 * L : L + 1;       // epilogue phases per tile
+  const int pair_stride = NSLOT * (int)gridDim.x;
 
+  constexpr int NEW = NSLOT * G::NEPI / 32;                  // epilogue warps (all groups)
   if (G::REGSHIFT && MODE != MODE_LOSS) {
-    if (warp < G::NEPI / 32) setmaxnreg_inc<232>(); else setmaxnreg_dec<40>();
+    if (warp < NEW) setmaxnreg_inc<G::EPI_REGS>(); else setmaxnreg_dec<G::CTL_REGS>();
   }
-  if (warp < G::NEPI / 32) {
-    // ===== epilogue warps =====
+  if (warp < NEW) {
+    // ===== epilogue warps: group `slot` walks ITS tiles (t0 + slot * gridDim.x of every pair) phase by phase, on its own
+    // operand buffer / accumulator columns / barriers; the two groups only share the MMA warp and the weight ring =====
+    const int slot = warp / (G::NEPI / 32);
     int seq = 0; uint32_t dpar = 0;
     const int* wshift = p.wshift + (size_t)task * p.wshift_stride;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    for (int t = blockIdx.x + slot * (int)gridDim.x; t < n_tiles; t += pair_stride) {
       int s = 0;
       while (s + 1 < kp.n_seg && t >= kp.seg_tile_begin[s + 1]) ++s;
       const int tile = t - kp.seg_tile_begin[s];
       const SegDesc& sg = kp.seg[s];
-      if (PDE == PDE_POISSON) {
-        if (sg.head == HEAD_POISSON_DOMAIN) TcTile<W, HEAD_POISSON_DOMAIN, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-        else TcTile<W, HEAD_POISSON_BOUNDARY, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-      } else if (PDE == PDE_BURGERS) {
-        if (sg.head == HEAD_BURGERS_DOMAIN) TcTile<W, HEAD_BURGERS_DOMAIN, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-        else TcTile<W, HEAD_BURGERS_IC, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-      } else if (PDE == PDE_HYPER) {
-        if (sg.head == HEAD_HYPER_DOMAIN) TcTile<W, HEAD_HYPER_DOMAIN, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-        else if (sg.head == HEAD_HYPER_TOP) TcTile<W, HEAD_HYPER_TOP, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-        else TcTile<W, HEAD_HYPER_BOTTOM, MODE>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-      } else if (PDE == PDE_EVAL1) {
-        TcTile<W, HEAD_EVAL, MODE_LOSS>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-      } else {
-        TcTile<W, HEAD_EVAL2, MODE_LOSS>::run(p, cx, sg, s, task, tile, tbase, seq, dpar, wshift);
-      }
-    }
-  } else if (warp == G::NEPI / 32) {
-    // ===== producer: stream the weight image through the ring (same stream for every tile) =====
-    if (lane == 0) {
-      const uint8_t* img = p.wimg + (size_t)task * p.wimg_stride;
-      uint32_t stage = 0, phase = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        for (int i = 0; i < nst_tile; ++i) {
-          mbar_wait(&cx.empty[stage], phase ^ 1u);
-          mbar_arrive_expect_tx(&cx.full[stage], STAGE_BYTES);
-          bulk_g2s(cx.ring + (size_t)stage * STAGE_BYTES, img + (size_t)i * STAGE_BYTES, STAGE_BYTES, &cx.full[stage]);
-          if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
+      MPDE_NOUNROLL
+      for (int ph = 0; ph < nph; ++ph) {
+        if (PDE == PDE_POISSON) {
+          if (sg.head == HEAD_POISSON_DOMAIN) TcTile<W, HEAD_POISSON_DOMAIN, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+          else TcTile<W, HEAD_POISSON_BOUNDARY, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+        } else if (PDE == PDE_BURGERS) {
+          if (sg.head == HEAD_BURGERS_DOMAIN) TcTile<W, HEAD_BURGERS_DOMAIN, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+          else TcTile<W, HEAD_BURGERS_IC, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+        } else if (PDE == PDE_HYPER) {
+          if (sg.head == HEAD_HYPER_DOMAIN) TcTile<W, HEAD_HYPER_DOMAIN, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+          else if (sg.head == HEAD_HYPER_TOP) TcTile<W, HEAD_HYPER_TOP, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+          else TcTile<W, HEAD_HYPER_BOTTOM, MODE>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+        } else if (PDE == PDE_EVAL1) {
+          TcTile<W, HEAD_EVAL, MODE_LOSS>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
+        } else {
+          TcTile<W, HEAD_EVAL2, MODE_LOSS>::phase(p, cx, sg, s, task, tile, slot, ph, tbase, seq, dpar, wshift);
         }
       }
     }
-  } else if (warp == G::NEPI / 32 + 1) {
+  } else if (warp == NEW) {
+    // ===== producer: per pair of tiles and contraction step, the step's stages once per active slot =====
+    if (lane == 0) {
+      const uint8_t* img = p.wimg + (size_t)task * p.wimg_stride;
+      uint32_t stage = 0, phase = 0;
+      for (int t0 = blockIdx.x; t0 < n_tiles; t0 += pair_stride) {
+        const int nsl = (t0 + (int)gridDim.x < n_tiles) ? NSLOT : 1;
+        for (int step = 1; step <= nsteps; ++step) {
+          const int first = tc_step_first_stage<W>(step, L);
+          const int cnt = (step != L) ? G::NMT * G::KSL : G::KSL;
+          (void)nsl;                                   // both slots of a pair share ONE pass over the step's stages
+          for (int i = 0; i < cnt; ++i) {
+            mbar_wait(&cx.empty[stage], phase ^ 1u);
+            mbar_arrive_expect_tx(&cx.full[stage], STAGE_BYTES);
+            bulk_g2s(cx.ring + (size_t)stage * STAGE_BYTES, img + (size_t)(first + i) * STAGE_BYTES, STAGE_BYTES, &cx.full[stage]);
+            if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == NEW + 1) {
     // ===== MMA issuer: the whole warp runs the loop (warp-uniform), one elected lane issues (see elect_one) =====
-    constexpr uint32_t idesc = make_idesc(FMT_F16, 128, TR, 0, 1);   // A (weights) K-major, B (jet rows) MN-major
+    // A (weights) K-major, B (jet rows) MN-major.  The two slots' operand buffers are the two 64-row blocks of ONE N = 128
+    // operand (block stride XBYTES), so a pair of tiles shares every weight stage and every MMA (an N = 64 MMA costs about
+    // as much as an N = 128 one: the A operand read from shared memory bounds it); a lone last tile runs at N = 64.
+    constexpr uint32_t idesc1 = make_idesc(FMT_F16, 128, TR, 0, 1), idesc2 = make_idesc(FMT_F16, 128, NSLOT * TR, 0, 1);
     constexpr uint32_t NBLK_BYTES = (uint32_t)W * 128u, LO_OFF = (uint32_t)(TR / 64) * NBLK_BYTES;
-    const uint32_t xb = smem_u32(cx.xbuf), ring0 = smem_u32(cx.ring);
-    const uint32_t bh_0 = desc_lo_mnmajor(xb, NBLK_BYTES), bl_0 = desc_lo_mnmajor(xb + LO_OFF, NBLK_BYTES);
-    uint32_t stage = 0, phase = 0, xpar = 0;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    const uint32_t xb = smem_u32(cx.xbuf0), ring0 = smem_u32(cx.ring);
+    const uint32_t bh_0 = desc_lo_mnmajor(xb, (uint32_t)G::XBYTES), bl_0 = desc_lo_mnmajor(xb + LO_OFF, (uint32_t)G::XBYTES);
+    uint32_t stage = 0, phase = 0, xpar0 = 0, xpar1 = 0;
+    for (int t0 = blockIdx.x; t0 < n_tiles; t0 += pair_stride) {
+      const int nsl = (t0 + (int)gridDim.x < n_tiles) ? NSLOT : 1;
+      const uint32_t idesc = nsl == NSLOT ? idesc2 : idesc1;
       for (int step = 1; step <= nsteps; ++step) {
-        mbar_wait(cx.xready, xpar); xpar ^= 1u;
-        tc_fence_after();
         const int nmt = (step != L) ? G::NMT : 1;   // step L is the output layer (one M tile)
+        mbar_wait(&cx.xready[0], xpar0); xpar0 ^= 1u;
+        if (nsl == NSLOT) { mbar_wait(&cx.xready[1], xpar1); xpar1 ^= 1u; }
+        tc_fence_after();
         for (int mt = 0; mt < nmt; ++mt) {
-          const uint32_t d = tbase + (uint32_t)mt * TR;
+          const uint32_t d = tbase + (uint32_t)mt * (NSLOT * TR);
           for (int s = 0; s < G::KSL; ++s) {
             mbar_wait(&cx.full[stage], phase);
             tc_fence_after();
@@ -658,28 +735,37 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
             if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
           }
         }
-        if (elect_one()) tc_commit(cx.dfull);            // one completion per contraction step: all M tiles
+        if (elect_one()) {                                  // one completion per contraction step and slot: all M tiles
+          tc_commit(&cx.dfull[0]);
+          if (nsl == NSLOT) tc_commit(&cx.dfull[1]);
+        }
         __syncwarp();
       }
     }
   }
-  else if (MODE != MODE_LOSS && warp == G::NEPI / 32 + 2) {
-    // ===== record prefetcher (see tc_hvp.cuh): asks L2 for the records of layer l one contraction step before the
-    // reverse pass reads them =====
+  else if (MODE != MODE_LOSS && warp == NEW + 2) {
+    // ===== record prefetcher: asks L2 for the records of layer l one contraction step before the reverse pass of the
+    // slot's tile reads them =====
     if (lane == 0) {
-      uint32_t xpar = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        int sgi = 0;
-        while (sgi + 1 < kp.n_seg && t >= kp.seg_tile_begin[sgi + 1]) ++sgi;
-        const int tile = t - kp.seg_tile_begin[sgi];
-        const int head = kp.seg[sgi].head;
-        const int jk = (head == HEAD_POISSON_DOMAIN) ? JET_LAP : (head == HEAD_BURGERS_DOMAIN) ? JET_XX : (head == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
-        const size_t per_layer = (size_t)rec_fields_points(jk) * W;           // floats of one (tile, layer) record block
-        const float* rec_tile = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[sgi] + (size_t)tile * L * per_layer;
+      uint32_t xpar0 = 0, xpar1 = 0;
+      for (int t0 = blockIdx.x; t0 < n_tiles; t0 += pair_stride) {
+        const int nsl = (t0 + (int)gridDim.x < n_tiles) ? NSLOT : 1;
         for (int step = 1; step <= nsteps; ++step) {
-          mbar_wait(cx.xready, xpar); xpar ^= 1u;
-          const int l = 2 * L - 2 - step;                // step L + j (j = 0 .. L-2) -> layer L-2-j
-          if (step >= L && l >= 0) bulk_prefetch_l2(rec_tile + (size_t)l * per_layer, (uint32_t)(per_layer * sizeof(float)));
+          for (int slot = 0; slot < nsl; ++slot) {
+            if (slot) { mbar_wait(&cx.xready[1], xpar1); xpar1 ^= 1u; } else { mbar_wait(&cx.xready[0], xpar0); xpar0 ^= 1u; }
+            const int l = 2 * L - 2 - step;                // step L + j (j = 0 .. L-2) -> layer L-2-j
+            if (step >= L && l >= 0) {
+              const int t = t0 + slot * (int)gridDim.x;
+              int sgi = 0;
+              while (sgi + 1 < kp.n_seg && t >= kp.seg_tile_begin[sgi + 1]) ++sgi;
+              const int tile = t - kp.seg_tile_begin[sgi];
+              const int head = kp.seg[sgi].head;
+              const int jk = (head == HEAD_POISSON_DOMAIN) ? JET_LAP : (head == HEAD_BURGERS_DOMAIN) ? JET_XX : (head == HEAD_HYPER_DOMAIN) ? JET_G : JET_V;
+              const size_t per_layer = (size_t)rec_fields_points(jk) * W;           // floats of one (tile, layer) record block
+              const float* rec_tile = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[sgi] + (size_t)tile * L * per_layer;
+              bulk_prefetch_l2(rec_tile + (size_t)l * per_layer, (uint32_t)(per_layer * sizeof(float)));
+            }
+          }
         }
       }
     }
@@ -688,7 +774,11 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
   if (warp == 0) tmem_dealloc(tbase, G::TMEM_COLS);
-  if (tid < MAX_SEG) kp.partial_terms[(size_t)cta * MAX_SEG + tid] = cx.terms[tid];
+  if (tid < MAX_SEG) {
+    float a = 0.f;
+    for (int sl = 0; sl < NSLOT; ++sl) a += cx.terms[sl * 4 + tid];
+    kp.partial_terms[(size_t)cta * MAX_SEG + tid] = a;
+  }
 }
 
 }  // namespace tc

@@ -28,7 +28,8 @@ MPDE_HD int ps_off_bias(int W, int l) { return 2 * W + l * W; }                 
 MPDE_HD int ps_off_wl(int W, int L) { return (L + 2) * W; }
 MPDE_HD int ps_count(int W, int L, int OUT) { return (L + 2) * W + W * OUT + OUT; }
 // floats of activation records per (tile, layer): NF * PTS * W
-MPDE_HD int rec_fields_points(int jk) { return jk == JET_V ? 2 * 128 : (jk == JET_G ? 4 * 32 : 5 * 32); }
+// (GRAD tiles: 64 rows = 16 jet points or 64 value points)
+MPDE_HD int rec_fields_points(int jk) { return jk == JET_V ? 2 * 64 : (jk == JET_G ? 4 * 16 : 5 * 16); }
 // HVP tiles (64 rows): saved fields + the tangent pre-activations zdot
 MPDE_HD int rec_fields_points_hvp(int jk) { return jk == JET_V ? 3 * 64 : (jk == JET_G ? 7 * 16 : 9 * 16); }
 
@@ -36,7 +37,7 @@ MPDE_HD int rec_fields_points_hvp(int jk) { return jk == JET_V ? 3 * 64 : (jk ==
 struct TcWgradParams {
   int W, L, T, n_seg;
   float omega;
-  int tile_rows;                            // jet rows per spilled tile: 128 (GRAD spills) or 64 (HVP spills)
+  int tile_rows;                            // jet rows per spilled tile (64: GRAD and HVP spills)
   int hvp_records;                          // records carry the tangent pre-activations zdot after the NF saved fields
   int want_hv;                              // 0: grad W_l = h^T zbar;  1: (H v)_W_l = hdot^T zbar + h^T zbardot
   int seg_tile_begin[MAX_SEG + 1];
