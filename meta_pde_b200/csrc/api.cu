@@ -229,7 +229,7 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
       pl->rec_per_task = off;
       pl->zsp_per_task = (long long)tiles * (pl->L - 1) * 64 * pl->W;   // tiles of 64 jet rows in both modes
       pl->PS = tc::ps_count(pl->W, pl->L, pl->OUT);
-      pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS * (mode == MODE_GRAD ? 2 : 1);   // GRAD: one partial per (CTA, epilogue group)
+      pl->n_rec = (size_t)T * off; pl->n_zsp = (size_t)T * pl->zsp_per_task; pl->n_psmall = ctas * pl->PS * 2;   // one partial per (CTA, epilogue group)
       {
         // tc_wgrad_kernel: one CTA per (task, layer, k tile) and row split; splits chosen to fill whole waves of the
         // SMs (512 items at T = 64: 3.46 waves -> 2 splits = 6.92; 64 items at T = 8: 0.43 -> 2 splits)
@@ -410,7 +410,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
       if (wprof) cudaEventRecord(ws, (cudaStream_t)stream);
       if (rc) return rc;
     }
-    rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G * (mode == MODE_GRAD ? 2 : 1), T, psmall, gout, pl.P, stream);
+    rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G * 2, T, psmall, gout, pl.P, stream);
     if (rc) return rc;
     if (mode == MODE_HVP) {
       wp.want_hv = 1; wp.gout = hv;
@@ -418,7 +418,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
       rc = tc_launch_wgrad(&wp, stream);
       if (wprof) cudaEventRecord(ws, (cudaStream_t)stream);
       if (rc) return rc;
-      rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G, T, psmall_h, hv, pl.P, stream);
+      rc = tc_launch_reduce_small(pl.W, pl.L, pl.OUT, pl.PS, pl.G * 2, T, psmall_h, hv, pl.P, stream);
       if (rc) return rc;
     }
   } else

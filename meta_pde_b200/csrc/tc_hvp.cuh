@@ -20,16 +20,20 @@ constexpr int HR = 64;                   // jet rows per HVP tile (MMA N)
 
 template <int W> struct HvGeo {
   static constexpr int NMT = W / 128, KSL = W / 64, NEPI = W;
-  // W = 256: 8 epilogue warps + one control warpgroup (producer warp, MMA warp, two idle warps).  The control warpgroup
-  // hands its registers to the epilogue warps (setmaxnreg): 12 warps launch at 168 registers, the epilogue then runs at
-  // 232 (no local-memory spills, deeper load batches) and the control warps at 40.
+  // Two epilogue GROUPS of W threads (thread = neuron): group g owns rows [32 g, 32 g + 32) of the tile -- the same MMAs,
+  // operand buffers and accumulators as before, twice the warps on the sin-jet algebra (round 2: an epilogue warp issued
+  // one instruction every ~5 cycles, a dependent chain; 2 warps per scheduler could not hide it).  + one control warpgroup
+  // (producer, MMA issuer, record prefetcher, one idle warp).  W = 256: 20 warps launch at 96 registers; the control
+  // warpgroup drops to 32 and the 16 epilogue warps rise to 112 (setmaxnreg: 128 x 64 = 512 x 16).
+  static constexpr int NG = 2, GR = HR / NG;            // groups, jet rows per group
   static constexpr bool REGSHIFT = (W == 256);
-  static constexpr int NT = REGSHIFT ? W + 128 : W + 96;   // + producer, MMA issuer and record-prefetch warps
+  static constexpr int EPI_REGS = 112, CTL_REGS = 32;
+  static constexpr int NT = NG * W + 128;
   static constexpr int SLAB = HR * 128;                 // [64 rows][64 k] fp16
   static constexpr int XBYTES = 2 * KSL * SLAB;         // hi slabs then lo slabs (one operand)
   static constexpr int RING = NSTAGE * STAGE_BYTES;
-  // misc: xs[2][HR], ybuf[HR][2], ydbuf[HR][2], red[HR] f32; cmax[2][8] u32; terms[4] f32; barriers; tmem slot
-  static constexpr int MISC = 2 * HR * 4 + 2 * HR * 4 + 2 * HR * 4 + HR * 4 + 64 + 16 + (2 * NSTAGE + 3) * 8 + 16;
+  // misc: xs[2][HR], ybuf[HR][2], ydbuf[HR][2], red[HR] f32; cmax[NG][2][8] u32; terms[4] f32; barriers; tmem slot
+  static constexpr int MISC = 2 * HR * 4 + 2 * HR * 4 + 2 * HR * 4 + HR * 4 + NG * 64 + 16 + (2 * NSTAGE + 3) * 8 + 16;
   static constexpr int SMEM = 2 * XBYTES + RING + MISC;
   static constexpr int TMEM_COLS = 512;                 // 3 accumulator sets x NMT x 64 columns (<= 384)
   // TMEM columns: per M tile mt the pair [W*primal (64) | W*tangent (64)] at mt * 128 -- one N = 128 MMA over the two
@@ -49,7 +53,7 @@ template <int W> struct HvCtx {
     xs = reinterpret_cast<float*>(ring + G::RING);
     ybuf = xs + 2 * HR; ydbuf = ybuf + 2 * HR; red = ydbuf + 2 * HR;
     cmax = reinterpret_cast<uint32_t*>(red + HR);
-    terms = reinterpret_cast<float*>(cmax + 16);
+    terms = reinterpret_cast<float*>(cmax + 16 * G::NG);
     full = reinterpret_cast<uint64_t*>(terms + 4);
     empty = full + NSTAGE; xready = empty + NSTAGE; dfull = xready + 1;
     tmem_slot = reinterpret_cast<uint32_t*>(dfull + 2);
@@ -122,9 +126,10 @@ struct HvTile {
     *reinterpret_cast<float4*>(xb + ((r0 & 4) ? LO_OFF : 0u) + chunk_off(r0 >> 3, n)) = make_float4(a, b, c, d);
   }
   // all 64 staged rows of neuron n -> fp16 hi / lo operand, scaled by ys[channel]
-  static TC_DEV void convert_rows(uint8_t* xb, int n, const float* ys) {
+  static TC_DEV void convert_rows(uint8_t* xb, int n, int grp, const float* ys) {
     MPDE_UNROLL
-    for (int j = 0; j < HR / 8; ++j) {
+    for (int jj = 0; jj < G::GR / 8; ++jj) {
+      const int j = grp * (G::GR / 8) + jj;             // this group's rows: chunks 4 g .. 4 g + 3
       const uint32_t o = chunk_off(j, n);
       const float4 a = *reinterpret_cast<const float4*>(xb + o);
       const float4 b = *reinterpret_cast<const float4*>(xb + LO_OFF + o);
@@ -143,33 +148,34 @@ struct HvTile {
   // fold the channel maxima (mx[0..3] primal, mx[4..7] tangent), barrier among the epilogue warps, read the shifts.
   // FWD: the primal value channel is sin: |a_0| <= 1, fixed shift 14.
   template <bool FWD>
-  static TC_DEV void agree_shifts(HvCtx<W>& cx, int& seq, const float (&mx)[8], float (&ys)[8], int (&sh)[8], int tid, int lane) {
-    uint32_t* cm = cx.cmax + (seq & 1) * 8;
+  static TC_DEV void agree_shifts(HvCtx<W>& cx, int grp, int& seq, const float (&mx)[8], float (&ys)[8], int (&sh)[8], int tid, int lane) {
+    uint32_t* cm = cx.cmax + grp * 16 + (seq & 1) * 8;
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) {
       const bool used = VAL ? (c == 4 || (!FWD && c == 0)) : ((c & 3) < C && !(FWD && c == 0));
       if (used) fold_max(cm + c, mx[c], lane);
     }
-    epi_sync<G::NEPI>();
+    epi_sync<G::NEPI>(grp);                             // the group's own barrier: its rows carry their own shifts
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) sh[c] = shift_for_max(__uint_as_float(cm[c]));
     if (FWD) sh[0] = 14;
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
     if (tid == 0) {
-      uint32_t* other = cx.cmax + ((seq & 1) ^ 1) * 8;
+      uint32_t* other = cx.cmax + grp * 16 + ((seq & 1) ^ 1) * 8;
       MPDE_UNROLL
       for (int c = 0; c < 8; ++c) other[c] = 0u;
     }
     ++seq;
   }
   // stage one point (CP = 4) / remember one value row (CP = 1: flushed every 4 points) and track the channel maxima
-  static TC_DEV void stage_point(uint8_t* xb, uint8_t* xdb, int pl, int n, const float* a, const float* ad, float (&mx)[8],
+  // `qs`: the point's index inside its unrolled group (compile-time at every call site; pl % 4 == qs % 4)
+  static TC_DEV void stage_point(uint8_t* xb, uint8_t* xdb, int pl, int qs, int n, const float* a, const float* ad, float (&mx)[8],
                                  float (&va)[4], float (&vd)[4]) {
     if (VAL) {
-      va[pl & 3] = a[0]; vd[pl & 3] = ad[0];
+      va[qs & 3] = a[0]; vd[qs & 3] = ad[0];
       mx[0] = fmaxf(mx[0], fabsf(a[0])); mx[4] = fmaxf(mx[4], fabsf(ad[0]));
-      if ((pl & 3) == 3) {
+      if ((qs & 3) == 3) {
         stage4(xb, pl - 3, n, va[0], va[1], va[2], va[3]);
         stage4(xdb, pl - 3, n, vd[0], vd[1], vd[2], vd[3]);
       }
@@ -181,13 +187,18 @@ struct HvTile {
     }
   }
 
-  // ---- the epilogue side of one tile (all W epilogue threads) ------------------------------------------
+  // barrier among ALL epilogue threads (both groups): named barrier 3
+  static TC_DEV void all_sync() { asm volatile("bar.sync 3, %0;" ::"n"(G::NG * G::NEPI) : "memory"); }
+
+  // ---- the epilogue side of one tile (both groups of W epilogue threads) --------------------------------
   static TC_DEV void run(const HvParams& hp, HvCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile,
                          uint32_t tbase, int& seq, uint32_t& dpar, const int* wshift, const int* wshift_d) {
     const TcParams& p = hp.t;
     const KParams& kp = p.k;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = tid, mt = n >> 7;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int grp = tid / G::NEPI;                      // epilogue group: rows [GR * grp, GR * grp + GR) of the tile
+    const int n = tid - grp * G::NEPI, mt = n >> 7;     // this thread's neuron
+    const int warp = n >> 5;                            // warp inside the group (groups start at multiples of 4 warps)
     const float om = kp.omega;
     const int L = kp.L;
     const float* th = kp.th + (size_t)task * kp.th_stride;
@@ -195,14 +206,17 @@ struct HvTile {
     const float* prm = kp.prm + (size_t)task * kp.nprm;
     const int pt0 = tile * PTS;
     const float* pts = sg.pts + (size_t)task * sg.task_stride;
-    const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), 0u);
+    const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)(grp * G::GR));
     const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR, c2 = (uint32_t)G::D2 + (uint32_t)mt * HR;   // accumulator columns
     float* xs = cx.xs;
     float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W +
              (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
-    constexpr int PPC = 16 / CP;                        // points per 16-column chunk
+    constexpr int TCH = 8;                              // accumulator columns per chunk (2 jet points: 112 registers)
+    constexpr int PPC = TCH / CP;                       // points per chunk
+    constexpr int PG = G::GR / CP;                      // points of one group
+    const int pg0 = grp * PG;                           // first point of this group
 
-    for (int i = tid; i < PTS; i += G::NEPI) {
+    for (int i = tid; i < PTS; i += G::NG * G::NEPI) {
       const int gp = pt0 + i;
       float x0 = 0.f, x1 = 0.f;
       if (gp < sg.n) { x0 = pts[2 * (size_t)gp]; x1 = pts[2 * (size_t)gp + 1]; }
@@ -214,10 +228,10 @@ struct HvTile {
     {
       const float w00 = mpde_ldg(th + n), w01 = mpde_ldg(th + W + n), b0 = mpde_ldg(th + 2 * W + n);
       const float d00 = mpde_ldg(thd + n), d01 = mpde_ldg(thd + W + n), db0 = mpde_ldg(thd + 2 * W + n);
-      epi_sync<G::NEPI>();                              // xs visible
+      all_sync();                                       // xs visible (written by threads of both groups)
       float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
       MPDE_NOUNROLL
-      for (int pl0 = 0; pl0 < PTS; pl0 += 4) {
+      for (int pl0 = pg0; pl0 < pg0 + PG; pl0 += 4) {
         MPDE_UNROLL
         for (int q = 0; q < 4; ++q) {
           const int pl = pl0 + q;
@@ -230,12 +244,12 @@ struct HvTile {
           for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) recp[(size_t)((NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
-          stage_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, mx, va, vd);
+          stage_point(cx.xbuf, cx.xdbuf, pl, q, n, a, ad, mx, va, vd);
         }
       }
-      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
-      convert_rows(cx.xbuf, n, ys);
-      convert_rows(cx.xdbuf, n, ys + 4);
+      agree_shifts<true>(cx, grp, seq, mx, ys, sh, n, lane);
+      convert_rows(cx.xbuf, n, grp, ys);
+      convert_rows(cx.xdbuf, n, grp, ys + 4);
     }
     fence_proxy_async_smem();
     tc_fence_before();
@@ -254,13 +268,13 @@ struct HvTile {
       tc_fence_after();
       float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
       MPDE_NOUNROLL
-      for (int ch = 0; ch < HR / 16; ++ch) {
-        uint32_t v0[16], v1[16], v2[16];
-        tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
+      for (int ch = 0; ch < G::GR / TCH; ++ch) {
+        uint32_t v0[TCH], v1[TCH], v2[TCH];
+        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1); tmem_ld8(tl + c2 + ch * TCH, v2);
         tmem_ld_wait();
         MPDE_UNROLL
         for (int q = 0; q < PPC; ++q) {
-          const int pl = ch * PPC + q;
+          const int pl = pg0 + ch * PPC + q;
           float z[4] = {0.f, 0.f, 0.f, 0.f}, zd[4] = {0.f, 0.f, 0.f, 0.f}, a[4], ad[4], sv[5];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) {
@@ -274,12 +288,12 @@ struct HvTile {
           for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f)) * (PTS * W) + (pl) * 128] = sv[f];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
-          stage_point(cx.xbuf, cx.xdbuf, pl, n, a, ad, mx, va, vd);
+          stage_point(cx.xbuf, cx.xdbuf, pl, q, n, a, ad, mx, va, vd);
         }
       }
-      agree_shifts<true>(cx, seq, mx, ys, sh, tid, lane);
-      convert_rows(cx.xbuf, n, ys);
-      convert_rows(cx.xdbuf, n, ys + 4);
+      agree_shifts<true>(cx, grp, seq, mx, ys, sh, n, lane);
+      convert_rows(cx.xbuf, n, grp, ys);
+      convert_rows(cx.xdbuf, n, grp, ys + 4);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(cx.xready);
@@ -294,23 +308,25 @@ struct HvTile {
         const int sw = wshift[L], swd = wshift_d[L];
         for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
       }
+      // each group's first warp: the output rows of ITS rows (descaled with the group's own shifts)
       MPDE_NOUNROLL
-      for (int ch = 0; ch < HR / 16; ++ch) {
-        uint32_t v0[16], v1[16], v2[16];
-        tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
+      for (int ch = 0; ch < G::GR / TCH; ++ch) {
+        uint32_t v0[TCH], v1[TCH], v2[TCH];
+        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1); tmem_ld8(tl + c2 + ch * TCH, v2);
         tmem_ld_wait();
         if (lane < OUT) {
           MPDE_UNROLL
-          for (int q = 0; q < 16; ++q) {
+          for (int q = 0; q < TCH; ++q) {
             const int c = VAL ? 0 : (q & 3);
-            cx.ybuf[(ch * 16 + q) * 2 + lane] = __uint_as_float(v0[q]) * zs[c];
-            cx.ydbuf[(ch * 16 + q) * 2 + lane] = fmaf(__uint_as_float(v1[q]), zs1[c], __uint_as_float(v2[q]) * zs2[c]);
+            const int r = grp * G::GR + ch * TCH + q;
+            cx.ybuf[r * 2 + lane] = __uint_as_float(v0[q]) * zs[c];
+            cx.ydbuf[r * 2 + lane] = fmaf(__uint_as_float(v1[q]), zs1[c], __uint_as_float(v2[q]) * zs2[c]);
           }
         }
       }
     }
     tc_fence_before();
-    epi_sync<G::NEPI>();
+    all_sync();
 
     // ---- head: value, seeds ybar and their tangents ybardot ----
     if (tid < PTS) {
@@ -340,8 +356,8 @@ struct HvTile {
           cx.ydbuf[(CP * pl + c) * 2 + o] = (valid && c < C) ? ubd[o * C + c] : 0.f;
         }
     }
-    epi_sync<G::NEPI>();
-    if (warp == 0) {
+    all_sync();
+    if (tid < 32) {
       float s = 0.f;
       MPDE_UNROLL
       for (int j = 0; j < (PTS + 31) / 32; ++j) s += (lane + 32 * j < PTS) ? cx.red[lane + 32 * j] : 0.f;
@@ -351,140 +367,172 @@ struct HvTile {
     }
 
     // ==================== reverse pass and its tangent ====================
+    // one instantiation per layer kind (l = L-1: seeds, no accumulators / 0 < l < L-1 / l = 0: no X to build): no runtime
+    // branch inside the per-point loops (round 2: the in-loop `l == ...` tests cost 11 % of the GRAD kernel)
+    int shz[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    reverse_layer<RK_LAST>(hp, cx, sg, seg_id, task, tile, tbase, L - 1, recp, shz, seq, dpar, wshift, wshift_d);
+    for (int l = L - 2; l >= 1; --l)
+      reverse_layer<RK_MID>(hp, cx, sg, seg_id, task, tile, tbase, l, recp, shz, seq, dpar, wshift, wshift_d);
+    reverse_layer<RK_FIRST>(hp, cx, sg, seg_id, task, tile, tbase, 0, recp, shz, seq, dpar, wshift, wshift_d);
+  }
+
+  enum { RK_LAST = 0, RK_MID = 1, RK_FIRST = 2 };
+  template <int RK>
+  static TC_DEV void reverse_layer(const HvParams& hp, HvCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile,
+                                   uint32_t tbase, int l, const float* recp, int (&shz)[8], int& seq, uint32_t& dpar,
+                                   const int* wshift, const int* wshift_d) {
+    constexpr bool LAST = (RK == RK_LAST), FIRST = (RK == RK_FIRST);
+    const TcParams& p = hp.t;
+    const KParams& kp = p.k;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int grp = tid / G::NEPI;
+    const int n = tid - grp * G::NEPI, mt = n >> 7;
+    const int warp = n >> 5;
+    const float om = kp.omega;
+    const int L = kp.L;
+    const float* th = kp.th + (size_t)task * kp.th_stride;
+    const float* thd = kp.thd + (size_t)task * kp.thd_stride;
+    const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)(grp * G::GR));
+    const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR, c2 = (uint32_t)G::D2 + (uint32_t)mt * HR;   // accumulator columns
+    float* xs = cx.xs;
+    constexpr int TCH = 8, PPC = TCH / CP, PG = G::GR / CP;
+    const int pg0 = grp * PG;
     const bool wg = hp.want_grad != 0;
-    float* psg = p.psmall + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
-    float* psh = hp.psmall_h + ((size_t)task * gridDim.x + blockIdx.x) * p.PS;
-    const size_t zoff = (size_t)task * p.zsp_task_stride + (size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) * HR * W + n;
-    float* zsp_tile = p.zsp + zoff;
-    float* zspd_tile = hp.zspd + zoff;
+    // per (CTA, group) partials of the small parameters: both groups own a thread for neuron n
+    const size_t pso = (((size_t)task * gridDim.x + blockIdx.x) * G::NG + grp) * p.PS;
+    float* psg = p.psmall + pso;
+    float* psh = hp.psmall_h + pso;
     float wl[OUT], wld[OUT];
     MPDE_UNROLL
-    for (int o = 0; o < OUT; ++o) {
-      wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
-      wld[o] = mpde_ldg(thd + ph_off_out(W, L) + n * OUT + o);
-    }
-    if (tid < OUT) {
-      float g = 0.f, h = 0.f;
-      for (int pl = 0; pl < PTS; ++pl) { g += cx.ybuf[(CP * pl) * 2 + tid]; h += cx.ydbuf[(CP * pl) * 2 + tid]; }
-      psh[ps_off_wl(W, L) + W * OUT + tid] += h;
-      if (wg) psg[ps_off_wl(W, L) + W * OUT + tid] += g;
-    }
-    int shz[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int l = L - 1; l >= 0; --l) {
-      float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f}, zs2[4] = {0.f, 0.f, 0.f, 0.f};
-      // the first chunk's record loads are issued before the accumulator wait (they do not depend on it)
-      float svb[PPC][NF + C];
+    for (int o = 0; o < OUT; ++o) { wl[o] = 0.f; wld[o] = 0.f; }
+    if (LAST) {
       MPDE_UNROLL
-      for (int q = 0; q < PPC; ++q)
-        MPDE_UNROLL
-        for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + (q) * 128];
-      if (l < L - 1) {
-        const int sw = wshift[l + 1], swd = wshift_d[l + 1];
-        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-shz[c] - sw); zs1[c] = pow2i(-shz[4 + c] - sw); zs2[c] = pow2i(-shz[c] - swd); }
-        mbar_wait(cx.dfull, dpar); dpar ^= 1u;           // all adjoint MMAs that read X / Xd have completed
-        tc_fence_after();
+      for (int o = 0; o < OUT; ++o) {
+        wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
+        wld[o] = mpde_ldg(thd + ph_off_out(W, L) + n * OUT + o);
       }
-      float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
-      float bsum = 0.f, bsumd = 0.f, g0 = 0.f, g1 = 0.f, h0 = 0.f, h1 = 0.f, gw[OUT], hw[OUT];
+      if (tid < OUT) {                                  // group 0 only: the whole tile's seeds
+        float g = 0.f, h = 0.f;
+        for (int pl = 0; pl < PTS; ++pl) { g += cx.ybuf[(CP * pl) * 2 + tid]; h += cx.ydbuf[(CP * pl) * 2 + tid]; }
+        psh[ps_off_wl(W, L) + W * OUT + tid] += h;
+        if (wg) psg[ps_off_wl(W, L) + W * OUT + tid] += g;
+      }
+    }
+    const float* rl = recp + (size_t)l * NFT * (PTS * W);   // this layer's records: [field][k tile][point][128]
+    float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f}, zs2[4] = {0.f, 0.f, 0.f, 0.f};
+    // the first chunk's record loads are issued before the accumulator wait (they do not depend on it)
+    float svb[PPC][NF + C];
+    MPDE_UNROLL
+    for (int q = 0; q < PPC; ++q)
       MPDE_UNROLL
-      for (int o = 0; o < OUT; ++o) { gw[o] = 0.f; hw[o] = 0.f; }
-      float* zl = zsp_tile + (size_t)(l - 1) * HR * W;       // only dereferenced for l >= 1
-      float* zld = zspd_tile + (size_t)(l - 1) * HR * W;
-      MPDE_NOUNROLL
-      for (int ch = 0; ch < HR / 16; ++ch) {
-        uint32_t v0[16], v1[16], v2[16];
-        if (l < L - 1) {
-          tmem_ld16(tl + c0 + ch * 16, v0); tmem_ld16(tl + c1 + ch * 16, v1); tmem_ld16(tl + c2 + ch * 16, v2);
-          tmem_ld_wait();
-        }
+      for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[f * (PTS * W) + (pg0 + q) * 128];
+    if (!LAST) {
+      const int sw = wshift[l + 1], swd = wshift_d[l + 1];
+      for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-shz[c] - sw); zs1[c] = pow2i(-shz[4 + c] - sw); zs2[c] = pow2i(-shz[c] - swd); }
+      mbar_wait(cx.dfull, dpar); dpar ^= 1u;           // all adjoint MMAs that read X / Xd have completed
+      tc_fence_after();
+    }
+    float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
+    float bsum = 0.f, bsumd = 0.f, g0 = 0.f, g1 = 0.f, h0 = 0.f, h1 = 0.f, gw[OUT], hw[OUT];
+    MPDE_UNROLL
+    for (int o = 0; o < OUT; ++o) { gw[o] = 0.f; hw[o] = 0.f; }
+    const size_t zoff = (size_t)task * p.zsp_task_stride +
+                        ((size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) + (FIRST ? 0 : l - 1)) * HR * W + n;
+    float* zl = p.zsp + zoff;                              // only dereferenced for l >= 1
+    float* zld = hp.zspd + zoff;
+    MPDE_NOUNROLL
+    for (int ch = 0; ch < G::GR / TCH; ++ch) {
+      uint32_t v0[TCH], v1[TCH], v2[TCH];
+      if (!LAST) {
+        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1); tmem_ld8(tl + c2 + ch * TCH, v2);
+        tmem_ld_wait();
+      }
+      const int chn = (ch + 1 < G::GR / TCH) ? ch + 1 : ch;   // next chunk's records (clamped: a repeated valid load, no branch)
+      MPDE_UNROLL
+      for (int q = 0; q < PPC; ++q) {
+        const int pl = pg0 + ch * PPC + q;
+        float ab[4] = {0.f, 0.f, 0.f, 0.f}, abd[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zd[4] = {0.f, 0.f, 0.f, 0.f};
+        float zb[4] = {0.f, 0.f, 0.f, 0.f}, zbd[4] = {0.f, 0.f, 0.f, 0.f};
         MPDE_UNROLL
-        for (int q = 0; q < PPC; ++q) {
-          const int pl = ch * PPC + q;
-          float ab[4] = {0.f, 0.f, 0.f, 0.f}, abd[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zd[4] = {0.f, 0.f, 0.f, 0.f};
-          float zb[4] = {0.f, 0.f, 0.f, 0.f}, zbd[4] = {0.f, 0.f, 0.f, 0.f};
-          MPDE_UNROLL
-          for (int c = 0; c < C; ++c) {
-            if (l < L - 1) {
-              ab[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
-              abd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
-            } else {
-              float a_ = 0.f, ad_ = 0.f;
-              MPDE_UNROLL
-              for (int o = 0; o < OUT; ++o) {
-                const float yb = cx.ybuf[(CP * pl + c) * 2 + o], ybd = cx.ydbuf[(CP * pl + c) * 2 + o];
-                a_ = fmaf(wl[o], yb, a_);
-                ad_ = fmaf(wl[o], ybd, fmaf(wld[o], yb, ad_));
-              }
-              ab[c] = a_; abd[c] = ad_;
-            }
-          }
-          MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) sv[f] = svb[q][f];
-          MPDE_UNROLL
-          for (int c = 0; c < C; ++c) zd[c] = svb[q][NF + c];
-          // this slot's record of the NEXT chunk: in flight while the chunk is processed
-          if (ch + 1 < HR / 16) {
-            MPDE_UNROLL
-            for (int f = 0; f < NF + C; ++f) svb[q][f] = recp[(size_t)((l * NFT + f)) * (PTS * W) + ((ch + 1) * PPC + q) * 128];
-          }
-          jet_act_bwd<JK>(om, sv, ab, zb);
-          jet_act_bwd_tan<JK>(om, sv, zd, ab, abd, zbd);
-          bsum += zb[0]; bsumd += zbd[0];
-          if (l == L - 1) {
-            float a[4], ad[4];
-            jet_act_from_saved<JK>(om, sv, a);
-            jet_act_tan<JK>(om, sv, zd, ad);
-            MPDE_UNROLL
-            for (int o = 0; o < OUT; ++o)
-              MPDE_UNROLL
-              for (int c = 0; c < C; ++c) {
-                const float yb = cx.ybuf[(CP * pl + c) * 2 + o], ybd = cx.ydbuf[(CP * pl + c) * 2 + o];
-                gw[o] = fmaf(a[c], yb, gw[o]);
-                hw[o] = fmaf(ad[c], yb, fmaf(a[c], ybd, hw[o]));
-              }
-          }
-          if (l == 0) {
-            if (VAL) {
-              g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[HR + pl], zb[0], g1);
-              h0 = fmaf(xs[pl], zbd[0], h0); h1 = fmaf(xs[HR + pl], zbd[0], h1);
-            } else {
-              g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[HR + pl], zb[0], zb[2]);
-              h0 += fmaf(xs[pl], zbd[0], zbd[1]); h1 += fmaf(xs[HR + pl], zbd[0], zbd[2]);
-            }
+        for (int c = 0; c < C; ++c) {
+          if (!LAST) {
+            ab[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
+            abd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
           } else {
-            // fp32 spill for tc_wgrad_kernel (written once, never read back here) + the staged copy for the next contraction
+            float a_ = 0.f, ad_ = 0.f;
             MPDE_UNROLL
-            for (int c = 0; c < CP; ++c) {
-              zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;
-              zld[(size_t)(CP * pl + c) * W] = c < C ? zbd[c] : 0.f;
+            for (int o = 0; o < OUT; ++o) {
+              const float yb = cx.ybuf[(CP * pl + c) * 2 + o], ybd = cx.ydbuf[(CP * pl + c) * 2 + o];
+              a_ = fmaf(wl[o], yb, a_);
+              ad_ = fmaf(wl[o], ybd, fmaf(wld[o], yb, ad_));
             }
-            stage_point(cx.xbuf, cx.xdbuf, pl, n, zb, zbd, mx, va, vd);
+            ab[c] = a_; abd[c] = ad_;
           }
         }
-      }
-      psh[ps_off_bias(W, l) + n] += bsumd;
-      if (wg) psg[ps_off_bias(W, l) + n] += bsum;
-      if (l == L - 1) {
         MPDE_UNROLL
-        for (int o = 0; o < OUT; ++o) {
-          psh[ps_off_wl(W, L) + n * OUT + o] += hw[o];
-          if (wg) psg[ps_off_wl(W, L) + n * OUT + o] += gw[o];
+        for (int f = 0; f < NF; ++f) sv[f] = svb[q][f];
+        MPDE_UNROLL
+        for (int c = 0; c < C; ++c) zd[c] = svb[q][NF + c];
+        // this slot's record of the NEXT chunk: in flight while the chunk is processed
+        MPDE_UNROLL
+        for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[f * (PTS * W) + (pg0 + chn * PPC + q) * 128];
+        jet_act_bwd<JK>(om, sv, ab, zb);
+        jet_act_bwd_tan<JK>(om, sv, zd, ab, abd, zbd);
+        bsum += zb[0]; bsumd += zbd[0];
+        if (LAST) {
+          float a[4], ad[4];
+          jet_act_from_saved<JK>(om, sv, a);
+          jet_act_tan<JK>(om, sv, zd, ad);
+          MPDE_UNROLL
+          for (int o = 0; o < OUT; ++o)
+            MPDE_UNROLL
+            for (int c = 0; c < C; ++c) {
+              const float yb = cx.ybuf[(CP * pl + c) * 2 + o], ybd = cx.ydbuf[(CP * pl + c) * 2 + o];
+              gw[o] = fmaf(a[c], yb, gw[o]);
+              hw[o] = fmaf(ad[c], yb, fmaf(a[c], ybd, hw[o]));
+            }
+        }
+        if (FIRST) {
+          if (VAL) {
+            g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[HR + pl], zb[0], g1);
+            h0 = fmaf(xs[pl], zbd[0], h0); h1 = fmaf(xs[HR + pl], zbd[0], h1);
+          } else {
+            g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[HR + pl], zb[0], zb[2]);
+            h0 += fmaf(xs[pl], zbd[0], zbd[1]); h1 += fmaf(xs[HR + pl], zbd[0], zbd[2]);
+          }
+        } else {
+          // fp32 spill for tc_wgrad_kernel (written once, never read back here) + the staged copy for the next contraction
+          MPDE_UNROLL
+          for (int c = 0; c < CP; ++c) {
+            zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;
+            zld[(size_t)(CP * pl + c) * W] = c < C ? zbd[c] : 0.f;
+          }
+          stage_point(cx.xbuf, cx.xdbuf, pl, q, n, zb, zbd, mx, va, vd);
         }
       }
-      if (l == 0) {
-        psh[n] += h0; psh[W + n] += h1;
-        if (wg) { psg[n] += g0; psg[W + n] += g1; }
-        epi_sync<G::NEPI>();                              // xs / ybuf are rewritten by the next tile
-        break;
-      }
-      float ysz[8];
-      agree_shifts<false>(cx, seq, mx, ysz, shz, tid, lane);
-      convert_rows(cx.xbuf, n, ysz);
-      convert_rows(cx.xdbuf, n, ysz + 4);
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(cx.xready);
     }
+    psh[ps_off_bias(W, l) + n] += bsumd;
+    if (wg) psg[ps_off_bias(W, l) + n] += bsum;
+    if (LAST) {
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o) {
+        psh[ps_off_wl(W, L) + n * OUT + o] += hw[o];
+        if (wg) psg[ps_off_wl(W, L) + n * OUT + o] += gw[o];
+      }
+    }
+    if (FIRST) {
+      psh[n] += h0; psh[W + n] += h1;
+      if (wg) { psg[n] += g0; psg[W + n] += g1; }
+      all_sync();                                       // xs / ybuf are rewritten by the next tile
+      return;
+    }
+    float ysz[8];
+    agree_shifts<false>(cx, grp, seq, mx, ysz, shz, n, lane);
+    convert_rows(cx.xbuf, n, grp, ysz);
+    convert_rows(cx.xdbuf, n, grp, ysz + 4);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    mbar_arrive(cx.xready);
   }
 };
 
@@ -507,17 +555,17 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
   if (tid == 0) {
     if (smem_u32(tc_smem_raw) & 1023u) { printf("tc_hvp_kernel: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     for (int i = 0; i < NSTAGE; ++i) { mbar_init(&cx.full[i], 1); mbar_init(&cx.empty[i], 1); }
-    mbar_init(cx.xready, G::NEPI);
+    mbar_init(cx.xready, G::NG * G::NEPI);
     mbar_init(cx.dfull, 1);
     mbar_fence_init();
-    for (int i = 0; i < 16; ++i) cx.cmax[i] = 0u;
+    for (int i = 0; i < 16 * G::NG; ++i) cx.cmax[i] = 0u;
     for (int i = 0; i < MAX_SEG; ++i) cx.terms[i] = 0.f;
   }
   if (warp == 0) tmem_alloc(cx.tmem_slot, G::TMEM_COLS);
   {
-    float* psg = p.psmall + (size_t)cta * p.PS;
-    float* psh = hp.psmall_h + (size_t)cta * p.PS;
-    for (int i = tid; i < p.PS; i += G::NT) { psh[i] = 0.f; if (hp.want_grad) psg[i] = 0.f; }
+    float* psg = p.psmall + (size_t)cta * G::NG * p.PS;   // one partial per (CTA, epilogue group)
+    float* psh = hp.psmall_h + (size_t)cta * G::NG * p.PS;
+    for (int i = tid; i < G::NG * p.PS; i += G::NT) { psh[i] = 0.f; if (hp.want_grad) psg[i] = 0.f; }
   }
   tc_fence_before();
   __syncthreads();
@@ -527,10 +575,11 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
   const int nst_fwd = (L - 1) * PER + G::KSL;
   const int nsteps = 2 * L - 1;                              // L-1 hidden, output, L-1 adjoint contractions
 
+  constexpr int NEW = G::NG * G::NEPI / 32;                  // epilogue warps (both groups)
   if (G::REGSHIFT) {
-    if (warp < G::NEPI / 32) setmaxnreg_inc<232>(); else setmaxnreg_dec<40>();
+    if (warp < NEW) setmaxnreg_inc<G::EPI_REGS>(); else setmaxnreg_dec<G::CTL_REGS>();
   }
-  if (warp < G::NEPI / 32) {
+  if (warp < NEW) {
     int seq = 0; uint32_t dpar = 0;
     const int* wshift = p.wshift + (size_t)task * p.wshift_stride;
     const int* wshift_d = hp.wshift_d + (size_t)task * hp.wshift_d_stride;
@@ -551,7 +600,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
         else HvTile<W, HEAD_HYPER_BOTTOM>::run(hp, cx, sg, s, task, tile, tbase, seq, dpar, wshift, wshift_d);
       }
     }
-  } else if (warp == G::NEPI / 32) {
+  } else if (warp == NEW) {
     // ===== producer: per contraction and M tile, the stages of W then the stages of Wdot =====
     if (lane == 0) {
       const uint8_t* img = p.wimg + (size_t)task * p.wimg_stride;
@@ -574,7 +623,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
         }
       }
     }
-  } else if (warp == G::NEPI / 32 + 1) {
+  } else if (warp == NEW + 1) {
     // ===== MMA issuer: the whole warp runs the loop (warp-uniform), one elected lane issues =====
     constexpr uint32_t idesc = make_idesc(FMT_F16, 128, HR, 0, 1);       // A (weights) K-major, B (jet rows) MN-major
     constexpr uint32_t idesc2 = make_idesc(FMT_F16, 128, 2 * HR, 0, 1);  // N = 128: rows of X then rows of Xd
@@ -623,7 +672,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
       }
     }
   }
-  else if (warp == G::NEPI / 32 + 2) {
+  else if (warp == NEW + 2) {
     // ===== record prefetcher: the reverse pass reads the activation records of layer l one full contraction step after
     // this thread asked L2 for them (they were written ~100 us earlier and the per-SM share of L2 does not hold a
     // whole tile's spills: without the prefetch every batch of record loads pays an HBM round trip) =====

@@ -487,13 +487,34 @@ struct TcTile {
     // =====================================================================================================
     if (MODE == MODE_LOSS) return;
     const int l = 2 * L - 1 - ph;
+    // the layer kind is a template argument: no runtime branch inside the per-point loops
+    if (ph == L) reverse_layer<RK_LAST>(p, cx, sg, seg_id, task, tile, slot, l, tlane, recp, seq, dpar, wshift);
+    else if (l == 0) reverse_layer<RK_FIRST>(p, cx, sg, seg_id, task, tile, slot, l, tlane, recp, seq, dpar, wshift);
+    else reverse_layer<RK_MID>(p, cx, sg, seg_id, task, tile, slot, l, tlane, recp, seq, dpar, wshift);
+  }
+
+  enum { RK_LAST = 0, RK_MID = 1, RK_FIRST = 2 };   // layer L-1 (seeds, no accumulators) / 0 < l < L-1 / layer 0 (no X to build)
+  template <int RK>
+  static TC_DEV void reverse_layer(const TcParams& p, TcCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile, int slot,
+                                   int l, uint32_t tlane, const float* recp, int& seq, uint32_t& dpar, const int* wshift) {
+    constexpr bool LAST = (RK == RK_LAST), FIRST = (RK == RK_FIRST);
+    const KParams& kp = p.k;
+    const int tid = (int)threadIdx.x - slot * G::NEPI, lane = tid & 31;
+    const int n = tid;
+    const float om = kp.omega;
+    const int L = kp.L;
+    const float* th = kp.th + (size_t)task * kp.th_stride;
+    float* xs = cx.xs(slot);
+    float* ybuf = cx.ybuf(slot);
+    uint8_t* xbuf = cx.xbuf(slot);
+    uint32_t* cmx = cx.cmax(slot);
+    constexpr int NF = JT::NF;
+    constexpr int TCH = 16, PPC = TCH / CP, SB = PPC;
     float* ps = p.psmall + (((size_t)task * gridDim.x + blockIdx.x) * NSLOT + slot) * p.PS;   // per (CTA, slot) partial
-    float* zsp_tile = p.zsp + (size_t)task * p.zsp_task_stride +
-                      (size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) * TR * W + n;
     float wl[OUT];
     MPDE_UNROLL
     for (int o = 0; o < OUT; ++o) wl[o] = 0.f;
-    if (l == L - 1) {
+    if (LAST) {
       MPDE_UNROLL
       for (int o = 0; o < OUT; ++o) wl[o] = mpde_ldg(th + ph_off_out(W, L) + n * OUT + o);
       if (tid < OUT) {   // output bias: sum of the value-channel seeds
@@ -502,92 +523,88 @@ struct TcTile {
         ps[ps_off_wl(W, L) + W * OUT + tid] += g;
       }
     }
-    constexpr int SB = PPC;                             // points per batch of record loads (one chunk)
-    {
-      float zs[4] = {0.f, 0.f, 0.f, 0.f};
-      // the first batch of record loads is issued before the accumulator wait (it does not depend on it)
-      float svb[SB][NF];
+    const float* rl = recp + (size_t)l * NF * (PTS * W);       // this layer's records: [field][k tile][point][128]
+    float zs[4] = {0.f, 0.f, 0.f, 0.f};
+    // the first batch of record loads is issued before the accumulator wait (it does not depend on it)
+    float svb[SB][NF];
+    MPDE_UNROLL
+    for (int qq = 0; qq < SB; ++qq)
       MPDE_UNROLL
-      for (int qq = 0; qq < SB; ++qq)
-        MPDE_UNROLL
-        for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (qq) * 128];
-      if (l < L - 1) {
-        int shz[4];
-        prev_shifts<false>(cmx, seq, shz);
-        const int sw = wshift[l + 1];
-        for (int c = 0; c < 4; ++c) zs[c] = pow2i(-shz[c] - sw);
-        mbar_wait(dfull, dpar); dpar ^= 1u;             // all adjoint MMAs that read X have completed
-        tc_fence_after();
-      }
-      float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
-      float bsum = 0.f, g0 = 0.f, g1 = 0.f, gw[OUT];
-      MPDE_UNROLL
-      for (int o = 0; o < OUT; ++o) gw[o] = 0.f;
-      float* zl = zsp_tile + (size_t)(l - 1) * TR * W;     // only dereferenced for l >= 1
-      MPDE_NOUNROLL
-      for (int ch = 0; ch < TR / TCH; ++ch) {
-        uint32_t v[TCH];
-        if (l < L - 1) { tmem_ld16(tlane + ch * TCH, v); tmem_ld_wait(); }
-        MPDE_UNROLL
-        for (int q0 = 0; q0 < PPC; q0 += SB) {
-        MPDE_UNROLL
-        for (int qq = 0; qq < SB; ++qq) {
-          const int q = q0 + qq;
-          const int pl = ch * PPC + q;
-          float ab[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zb[4] = {0.f, 0.f, 0.f, 0.f};
-          MPDE_UNROLL
-          for (int c = 0; c < C; ++c) {
-            if (l < L - 1) {
-              ab[c] = __uint_as_float(v[CP * q + c]) * zs[c];
-            } else {
-              float a_ = 0.f;
-              MPDE_UNROLL
-              for (int o = 0; o < OUT; ++o) a_ = fmaf(wl[o], ybuf[(CP * pl + c) * 2 + o], a_);
-              ab[c] = a_;
-            }
-          }
-          MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) sv[f] = svb[qq][f];
-          // this slot's record of the NEXT batch: in flight while the batch is processed
-          if (pl + SB < PTS) {
-            MPDE_UNROLL
-            for (int f = 0; f < NF; ++f) svb[qq][f] = recp[(size_t)((l * NF + f)) * (PTS * W) + (pl + SB) * 128];
-          }
-          jet_act_bwd<JK>(om, sv, ab, zb);
-          bsum += zb[0];
-          if (l == L - 1) {
-            float a[4];
-            jet_act_from_saved<JK>(om, sv, a);
-            MPDE_UNROLL
-            for (int o = 0; o < OUT; ++o)
-              MPDE_UNROLL
-              for (int c = 0; c < C; ++c) gw[o] = fmaf(a[c], ybuf[(CP * pl + c) * 2 + o], gw[o]);
-          }
-          if (l == 0) {
-            if (VAL) { g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[TR + pl], zb[0], g1); }
-            else { g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[TR + pl], zb[0], zb[2]); }
-          } else {
-            MPDE_UNROLL
-            for (int c = 0; c < CP; ++c) zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;   // fp32 spill for tc_wgrad_kernel
-            stage_point(xbuf, pl, q, n, zb, mx, va);
-          }
-        }
-        }
-      }
-      // small-parameter gradients: owner-computes read-modify-write into this CTA's partial
-      ps[ps_off_bias(W, l) + n] += bsum;
-      if (l == L - 1) {
-        MPDE_UNROLL
-        for (int o = 0; o < OUT; ++o) ps[ps_off_wl(W, L) + n * OUT + o] += gw[o];
-      }
-      if (l == 0) { ps[n] += g0; ps[W + n] += g1; epi_sync<G::NEPI>(slot); return; }   // xs is rewritten by the slot's next tile
-      float ysz[4];
-      agree_shifts<false>(cmx, slot, seq, mx, ysz, tid, lane);
-      convert_rows(xbuf, n, ysz);
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(xready);
+      for (int f = 0; f < NF; ++f) svb[qq][f] = rl[f * (PTS * W) + qq * 128];
+    if (!LAST) {
+      int shz[4];
+      prev_shifts<false>(cmx, seq, shz);
+      const int sw = wshift[l + 1];
+      for (int c = 0; c < 4; ++c) zs[c] = pow2i(-shz[c] - sw);
+      mbar_wait(cx.dfull + slot, dpar); dpar ^= 1u;   // all adjoint MMAs that read X have completed
+      tc_fence_after();
     }
+    float mx[4] = {0.f, 0.f, 0.f, 0.f}, va[4];
+    float bsum = 0.f, g0 = 0.f, g1 = 0.f, gw[OUT];
+    MPDE_UNROLL
+    for (int o = 0; o < OUT; ++o) gw[o] = 0.f;
+    // zbar_l spill for tc_wgrad_kernel (layers >= 1)
+    float* zl = p.zsp + (size_t)task * p.zsp_task_stride +
+                ((size_t)(kp.seg_tile_begin[seg_id] + tile) * (L - 1) + (FIRST ? 0 : l - 1)) * TR * W + n;
+    MPDE_NOUNROLL
+    for (int ch = 0; ch < TR / TCH; ++ch) {
+      uint32_t v[TCH];
+      if (!LAST) { tmem_ld16(tlane + ch * TCH, v); tmem_ld_wait(); }
+      // next chunk's records (clamped on the last chunk: a repeated, valid load instead of a branch)
+      const int chn = (ch + 1 < TR / TCH) ? ch + 1 : ch;
+      MPDE_UNROLL
+      for (int q = 0; q < PPC; ++q) {
+        const int pl = ch * PPC + q;
+        float ab[4] = {0.f, 0.f, 0.f, 0.f}, sv[5], zb[4] = {0.f, 0.f, 0.f, 0.f};
+        MPDE_UNROLL
+        for (int c = 0; c < C; ++c) {
+          if (!LAST) {
+            ab[c] = __uint_as_float(v[CP * q + c]) * zs[c];
+          } else {
+            float a_ = 0.f;
+            MPDE_UNROLL
+            for (int o = 0; o < OUT; ++o) a_ = fmaf(wl[o], ybuf[(CP * pl + c) * 2 + o], a_);
+            ab[c] = a_;
+          }
+        }
+        MPDE_UNROLL
+        for (int f = 0; f < NF; ++f) sv[f] = svb[q][f];
+        // this slot's record of the NEXT chunk: in flight while the chunk is processed
+        MPDE_UNROLL
+        for (int f = 0; f < NF; ++f) svb[q][f] = rl[f * (PTS * W) + (chn * PPC + q) * 128];
+        jet_act_bwd<JK>(om, sv, ab, zb);
+        bsum += zb[0];
+        if (LAST) {
+          float a[4];
+          jet_act_from_saved<JK>(om, sv, a);
+          MPDE_UNROLL
+          for (int o = 0; o < OUT; ++o)
+            MPDE_UNROLL
+            for (int c = 0; c < C; ++c) gw[o] = fmaf(a[c], ybuf[(CP * pl + c) * 2 + o], gw[o]);
+        }
+        if (FIRST) {
+          if (VAL) { g0 = fmaf(xs[pl], zb[0], g0); g1 = fmaf(xs[TR + pl], zb[0], g1); }
+          else { g0 += fmaf(xs[pl], zb[0], zb[1]); g1 += fmaf(xs[TR + pl], zb[0], zb[2]); }
+        } else {
+          MPDE_UNROLL
+          for (int c = 0; c < CP; ++c) zl[(size_t)(CP * pl + c) * W] = c < C ? zb[c] : 0.f;   // fp32 spill for tc_wgrad_kernel
+          stage_point(xbuf, pl, q, n, zb, mx, va);
+        }
+      }
+    }
+    // small-parameter gradients: owner-computes read-modify-write into this (CTA, slot) partial
+    ps[ps_off_bias(W, l) + n] += bsum;
+    if (LAST) {
+      MPDE_UNROLL
+      for (int o = 0; o < OUT; ++o) ps[ps_off_wl(W, L) + n * OUT + o] += gw[o];
+    }
+    if (FIRST) { ps[n] += g0; ps[W + n] += g1; epi_sync<G::NEPI>(slot); return; }   // xs is rewritten by the slot's next tile
+    float ysz[4];
+    agree_shifts<false>(cmx, slot, seq, mx, ysz, tid, lane);
+    convert_rows(xbuf, n, ysz);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    mbar_arrive(cx.xready + slot);
   }
 };
 
