@@ -18,6 +18,12 @@ namespace tc {
 
 #define TC_DEV __device__ __forceinline__
 
+// The warp index as a value the compiler KNOWS to be warp-uniform (a shuffle result): role branches on it are uniform
+// branches, so code under them may keep uniform registers live.  With `threadIdx.x >> 5` ptxas treated every role region
+// as divergent and re-materialised the global-memory descriptor before each LDG / STG (2 R2UR per access: 9 % of the
+// HVP kernel's instructions, round 2).
+TC_DEV int warp_idx_uniform() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 TC_DEV uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 
 // ---- mbarrier ---------------------------------------------------------------------------------------

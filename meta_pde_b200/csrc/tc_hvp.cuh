@@ -196,9 +196,10 @@ struct HvTile {
     const TcParams& p = hp.t;
     const KParams& kp = p.k;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int grp = tid / G::NEPI;                      // epilogue group: rows [GR * grp, GR * grp + GR) of the tile
+    const int hwarp = warp_idx_uniform();
+    const int grp = hwarp / (G::NEPI / 32);             // epilogue group: rows [GR * grp, GR * grp + GR) of the tile
     const int n = tid - grp * G::NEPI, mt = n >> 7;     // this thread's neuron
-    const int warp = n >> 5;                            // warp inside the group (groups start at multiples of 4 warps)
+    const int warp = hwarp - grp * (G::NEPI / 32);      // warp inside the group (groups start at multiples of 4 warps)
     const float om = kp.omega;
     const int L = kp.L;
     const float* th = kp.th + (size_t)task * kp.th_stride;
@@ -385,9 +386,10 @@ struct HvTile {
     const TcParams& p = hp.t;
     const KParams& kp = p.k;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int grp = tid / G::NEPI;
+    const int hwarp = warp_idx_uniform();
+    const int grp = hwarp / (G::NEPI / 32);
     const int n = tid - grp * G::NEPI, mt = n >> 7;
-    const int warp = n >> 5;
+    const int warp = hwarp - grp * (G::NEPI / 32);
     const float om = kp.omega;
     const int L = kp.L;
     const float* th = kp.th + (size_t)task * kp.th_stride;
@@ -546,7 +548,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
   cx.carve();
   const TcParams& p = hp.t;
   const KParams& kp = p.k;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_idx_uniform(), lane = tid & 31;
   const int task = blockIdx.y;
   const int cta = blockIdx.y * gridDim.x + blockIdx.x;
   const int L = kp.L;

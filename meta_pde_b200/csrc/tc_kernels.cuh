@@ -303,7 +303,8 @@ struct TcTile {
   static TC_DEV void phase(const TcParams& p, TcCtx<W>& cx, const SegDesc& sg, int seg_id, int task, int tile, int slot,
                            int ph, uint32_t tbase, int& seq, uint32_t& dpar, const int* wshift) {
     const KParams& kp = p.k;
-    const int tid = (int)threadIdx.x - slot * G::NEPI, lane = tid & 31, warp = tid >> 5;   // indices inside the slot's group
+    const int tid = (int)threadIdx.x - slot * G::NEPI, lane = tid & 31;   // indices inside the slot's group
+    const int warp = warp_idx_uniform() - slot * (G::NEPI / 32);
     const int n = tid;                          // this thread's neuron
     const int mt = n >> 7;
     const float om = kp.omega;
@@ -630,7 +631,7 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
   TcCtx<W> cx;
   cx.carve();
   const KParams& kp = p.k;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_idx_uniform(), lane = tid & 31;
   const int task = blockIdx.y;
   const int cta = blockIdx.y * gridDim.x + blockIdx.x;
   const int L = kp.L;

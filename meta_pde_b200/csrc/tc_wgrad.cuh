@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
   uint64_t* dfull = op_full + 4;             // [2] MMA commit -> promotion
   uint64_t* dfree = op_full + 6;             // [2] promotion (512) -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + G::NBAR);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_idx_uniform(), lane = tid & 31;
   const int task = blockIdx.y;
   const int l = 1 + blockIdx.x / G::NMT, kt = blockIdx.x % G::NMT;
   const int L = p.L;
