@@ -35,10 +35,9 @@ template <int W> struct HvGeo {
   // misc: xs[2][HR], ybuf[HR][2], ydbuf[HR][2], red[HR] f32; cmax[NG][2][8] u32; terms[4] f32; barriers; tmem slot
   static constexpr int MISC = 2 * HR * 4 + 2 * HR * 4 + 2 * HR * 4 + HR * 4 + NG * 64 + 16 + (2 * NSTAGE + 3) * 8 + 16;
   static constexpr int SMEM = 2 * XBYTES + RING + MISC;
-  static constexpr int TMEM_COLS = 512;                 // 3 accumulator sets x NMT x 64 columns (<= 384)
-  // TMEM columns: per M tile mt the pair [W*primal (64) | W*tangent (64)] at mt * 128 -- one N = 128 MMA over the two
-  // row blocks X | Xd, which share the A operand -- then Wdot*primal at D2 + mt * 64
-  static constexpr int D2 = 2 * NMT * HR;
+  // TMEM columns: per M tile mt the pair [W*primal (64) | W*tangent + Wdot*primal (64)] at mt * 128: one N = 128 MMA over
+  // the two row blocks X | Xd, which share the A operand, then the N = 64 MMAs of Wdot * X accumulate into the tangent columns
+  static constexpr int TMEM_COLS = 2 * NMT * HR;        // 128 or 256
 };
 
 template <int W> struct HvCtx {
@@ -145,10 +144,16 @@ struct HvTile {
       *reinterpret_cast<uint4*>(xb + LO_OFF + o) = lv;
     }
   }
-  // fold the channel maxima (mx[0..3] primal, mx[4..7] tangent), barrier among the epilogue warps, read the shifts.
-  // FWD: the primal value channel is sin: |a_0| <= 1, fixed shift 14.
+  // fold the channel maxima (mx[0..3] primal, mx[4..7] tangent), barrier among the group's warps, read the shifts.
+  // FWD: the primal value channel is sin: |a_0| <= 1, shift at most 14.
+  // Shared exponent (round 2): W * tangent and Wdot * primal are accumulated in ONE set of accumulator columns, so their
+  // scales must agree: sh_tangent + sw = sh_primal + swd, i.e. sh_tangent = sh_primal + delta with delta = swd - sw of the
+  // contraction that consumes this operand.  Per channel e = min(max-safe tangent shift, max-safe primal shift + delta);
+  // tangent shift = e, primal shift = e - delta: never above a max-safe shift (no fp16 overflow); the operand that is
+  // scaled below its own optimum belongs to the term that is the smaller one at the common scale.
   template <bool FWD>
-  static TC_DEV void agree_shifts(HvCtx<W>& cx, int grp, int& seq, const float (&mx)[8], float (&ys)[8], int (&sh)[8], int tid, int lane) {
+  static TC_DEV void agree_shifts(HvCtx<W>& cx, int grp, int& seq, int delta, const float (&mx)[8], float (&ys)[8], int (&sh)[8],
+                                  int tid, int lane) {
     uint32_t* cm = cx.cmax + grp * 16 + (seq & 1) * 8;
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) {
@@ -157,8 +162,18 @@ struct HvTile {
     }
     epi_sync<G::NEPI>(grp);                             // the group's own barrier: its rows carry their own shifts
     MPDE_UNROLL
-    for (int c = 0; c < 8; ++c) sh[c] = shift_for_max(__uint_as_float(cm[c]));
-    if (FWD) sh[0] = 14;
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t mp = cm[c], md = cm[4 + c];
+      // an all-zero block puts no constraint on the common exponent
+      const int sp = (FWD && c == 0) ? 14 : (mp ? shift_for_max(__uint_as_float(mp)) : 100);
+      const int sd = md ? shift_for_max(__uint_as_float(md)) : 100;
+      int e = sp + delta < sd ? sp + delta : sd;
+      e = e < -90 ? -90 : (e > 90 ? 90 : e);
+      int ep = e - delta;
+      ep = ep < -90 ? -90 : (ep > 90 ? 90 : ep);
+      sh[4 + c] = ep + delta;                           // (clamped consistently: tangent = primal + delta)
+      sh[c] = ep;
+    }
     MPDE_UNROLL
     for (int c = 0; c < 8; ++c) ys[c] = pow2i(sh[c]);
     if (tid == 0) {
@@ -168,7 +183,6 @@ struct HvTile {
     }
     ++seq;
   }
-  // stage one point (CP = 4) / remember one value row (CP = 1: flushed every 4 points) and track the channel maxima
   // `qs`: the point's index inside its unrolled group (compile-time at every call site; pl % 4 == qs % 4)
   static TC_DEV void stage_point(uint8_t* xb, uint8_t* xdb, int pl, int qs, int n, const float* a, const float* ad, float (&mx)[8],
                                  float (&va)[4], float (&vd)[4]) {
@@ -208,7 +222,7 @@ struct HvTile {
     const int pt0 = tile * PTS;
     const float* pts = sg.pts + (size_t)task * sg.task_stride;
     const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)(grp * G::GR));
-    const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR, c2 = (uint32_t)G::D2 + (uint32_t)mt * HR;   // accumulator columns
+    const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR;   // accumulator columns: primal, tangent
     float* xs = cx.xs;
     float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W +
              (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
@@ -248,7 +262,7 @@ struct HvTile {
           stage_point(cx.xbuf, cx.xdbuf, pl, q, n, a, ad, mx, va, vd);
         }
       }
-      agree_shifts<true>(cx, grp, seq, mx, ys, sh, n, lane);
+      agree_shifts<true>(cx, grp, seq, wshift_d[1] - wshift[1], mx, ys, sh, n, lane);
       convert_rows(cx.xbuf, n, grp, ys);
       convert_rows(cx.xdbuf, n, grp, ys + 4);
     }
@@ -260,18 +274,18 @@ struct HvTile {
     for (int l = 1; l < L; ++l) {
       const float bias = mpde_ldg(th + ph_off_layer(W, l) + 2 * W * W + n);
       const float biasd = mpde_ldg(thd + ph_off_layer(W, l) + 2 * W * W + n);
-      float zs[4], zs1[4], zs2[4];
+      float zs[4], zs1[4];
       {
-        const int sw = wshift[l], swd = wshift_d[l];
-        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
+        const int sw = wshift[l];
+        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); }
       }
       mbar_wait(cx.dfull, dpar); dpar ^= 1u;             // every MMA of this layer has completed: X / Xd may be rewritten
       tc_fence_after();
       float mx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, va[4], vd[4];
       MPDE_NOUNROLL
       for (int ch = 0; ch < G::GR / TCH; ++ch) {
-        uint32_t v0[TCH], v1[TCH], v2[TCH];
-        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1); tmem_ld8(tl + c2 + ch * TCH, v2);
+        uint32_t v0[TCH], v1[TCH];
+        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1);
         tmem_ld_wait();
         MPDE_UNROLL
         for (int q = 0; q < PPC; ++q) {
@@ -280,7 +294,7 @@ struct HvTile {
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) {
             z[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
-            zd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
+            zd[c] = __uint_as_float(v1[CP * q + c]) * zs1[c];
           }
           z[0] += bias; zd[0] += biasd;
           jet_act_fwd<JK>(om, z, a, sv);
@@ -292,7 +306,7 @@ struct HvTile {
           stage_point(cx.xbuf, cx.xdbuf, pl, q, n, a, ad, mx, va, vd);
         }
       }
-      agree_shifts<true>(cx, grp, seq, mx, ys, sh, n, lane);
+      agree_shifts<true>(cx, grp, seq, wshift_d[l + 1] - wshift[l + 1], mx, ys, sh, n, lane);
       convert_rows(cx.xbuf, n, grp, ys);
       convert_rows(cx.xdbuf, n, grp, ys + 4);
       fence_proxy_async_smem();
@@ -304,16 +318,16 @@ struct HvTile {
     mbar_wait(cx.dfull, dpar); dpar ^= 1u;
     tc_fence_after();
     if (warp == 0) {
-      float zs[4], zs1[4], zs2[4];
+      float zs[4], zs1[4];
       {
-        const int sw = wshift[L], swd = wshift_d[L];
-        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); zs2[c] = pow2i(-sh[c] - swd); }
+        const int sw = wshift[L];
+        for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-sh[c] - sw); zs1[c] = pow2i(-sh[4 + c] - sw); }
       }
       // each group's first warp: the output rows of ITS rows (descaled with the group's own shifts)
       MPDE_NOUNROLL
       for (int ch = 0; ch < G::GR / TCH; ++ch) {
-        uint32_t v0[TCH], v1[TCH], v2[TCH];
-        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1); tmem_ld8(tl + c2 + ch * TCH, v2);
+        uint32_t v0[TCH], v1[TCH];
+        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1);
         tmem_ld_wait();
         if (lane < OUT) {
           MPDE_UNROLL
@@ -321,7 +335,7 @@ struct HvTile {
             const int c = VAL ? 0 : (q & 3);
             const int r = grp * G::GR + ch * TCH + q;
             cx.ybuf[r * 2 + lane] = __uint_as_float(v0[q]) * zs[c];
-            cx.ydbuf[r * 2 + lane] = fmaf(__uint_as_float(v1[q]), zs1[c], __uint_as_float(v2[q]) * zs2[c]);
+            cx.ydbuf[r * 2 + lane] = __uint_as_float(v1[q]) * zs1[c];
           }
         }
       }
@@ -395,7 +409,7 @@ struct HvTile {
     const float* th = kp.th + (size_t)task * kp.th_stride;
     const float* thd = kp.thd + (size_t)task * kp.thd_stride;
     const uint32_t tl = tmem_addr(tbase, 32u * (uint32_t)(warp & 3), (uint32_t)(grp * G::GR));
-    const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR, c2 = (uint32_t)G::D2 + (uint32_t)mt * HR;   // accumulator columns
+    const uint32_t c0 = (uint32_t)mt * 2u * HR, c1 = c0 + HR;   // accumulator columns: primal, tangent
     float* xs = cx.xs;
     constexpr int TCH = 8, PPC = TCH / CP, PG = G::GR / CP;
     const int pg0 = grp * PG;
@@ -421,7 +435,7 @@ struct HvTile {
       }
     }
     const float* rl = recp + (size_t)l * NFT * (PTS * W);   // this layer's records: [field][k tile][point][128]
-    float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f}, zs2[4] = {0.f, 0.f, 0.f, 0.f};
+    float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f};
     // the first chunk's record loads are issued before the accumulator wait (they do not depend on it)
     float svb[PPC][NF + C];
     MPDE_UNROLL
@@ -429,8 +443,8 @@ struct HvTile {
       MPDE_UNROLL
       for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[f * (PTS * W) + (pg0 + q) * 128];
     if (!LAST) {
-      const int sw = wshift[l + 1], swd = wshift_d[l + 1];
-      for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-shz[c] - sw); zs1[c] = pow2i(-shz[4 + c] - sw); zs2[c] = pow2i(-shz[c] - swd); }
+      const int sw = wshift[l + 1];
+      for (int c = 0; c < 4; ++c) { zs[c] = pow2i(-shz[c] - sw); zs1[c] = pow2i(-shz[4 + c] - sw); }
       mbar_wait(cx.dfull, dpar); dpar ^= 1u;           // all adjoint MMAs that read X / Xd have completed
       tc_fence_after();
     }
@@ -444,9 +458,9 @@ struct HvTile {
     float* zld = hp.zspd + zoff;
     MPDE_NOUNROLL
     for (int ch = 0; ch < G::GR / TCH; ++ch) {
-      uint32_t v0[TCH], v1[TCH], v2[TCH];
+      uint32_t v0[TCH], v1[TCH];
       if (!LAST) {
-        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1); tmem_ld8(tl + c2 + ch * TCH, v2);
+        tmem_ld8(tl + c0 + ch * TCH, v0); tmem_ld8(tl + c1 + ch * TCH, v1);
         tmem_ld_wait();
       }
       const int chn = (ch + 1 < G::GR / TCH) ? ch + 1 : ch;   // next chunk's records (clamped: a repeated valid load, no branch)
@@ -459,7 +473,7 @@ struct HvTile {
         for (int c = 0; c < C; ++c) {
           if (!LAST) {
             ab[c] = __uint_as_float(v0[CP * q + c]) * zs[c];
-            abd[c] = fmaf(__uint_as_float(v1[CP * q + c]), zs1[c], __uint_as_float(v2[CP * q + c]) * zs2[c]);
+            abd[c] = __uint_as_float(v1[CP * q + c]) * zs1[c];
           } else {
             float a_ = 0.f, ad_ = 0.f;
             MPDE_UNROLL
@@ -529,7 +543,7 @@ struct HvTile {
       return;
     }
     float ysz[8];
-    agree_shifts<false>(cx, grp, seq, mx, ysz, shz, n, lane);
+    agree_shifts<false>(cx, grp, seq, wshift_d[l] - wshift[l], mx, ysz, shz, n, lane);
     convert_rows(cx.xbuf, n, grp, ysz);
     convert_rows(cx.xdbuf, n, grp, ysz + 4);
     fence_proxy_async_smem();
@@ -642,7 +656,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
         tc_fence_after();
         const int nmt = (step != L) ? G::NMT : 1;
         for (int mt = 0; mt < nmt; ++mt) {
-          const uint32_t d01 = tbase + (uint32_t)mt * 2u * HR, d2 = tbase + G::D2 + (uint32_t)mt * HR;
+          const uint32_t d01 = tbase + (uint32_t)mt * 2u * HR, d2 = d01 + HR;   // Wdot * X accumulates into the tangent columns
           for (int which = 0; which < 2; ++which) {
             for (int s = 0; s < G::KSL; ++s) {
               mbar_wait(&cx.full[stage], phase);
@@ -659,7 +673,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
                     mma_f16_ss(d01, ah, bh2, idesc2, acc); mma_f16_ss(d01, al, bh2, idesc2, 1); mma_f16_ss(d01, ah, bl2, idesc2, 1);
                   } else {
                     const uint64_t bh = desc_join(bh_0 + koff + kk * 128), bl = desc_join(bl_0 + koff + kk * 128);
-                    mma_f16_ss(d2, ah, bh, idesc, acc); mma_f16_ss(d2, al, bh, idesc, 1); mma_f16_ss(d2, ah, bl, idesc, 1);   // Wdot * primal
+                    mma_f16_ss(d2, ah, bh, idesc, 1); mma_f16_ss(d2, al, bh, idesc, 1); mma_f16_ss(d2, ah, bl, idesc, 1);   // += Wdot * primal
                   }
                 }
                 tc_commit(&cx.empty[stage]);
