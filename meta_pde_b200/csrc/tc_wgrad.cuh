@@ -276,50 +276,30 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
       __syncwarp();
     }
   } else {
-    // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lanes 1..: one record field each).
-    // The ring holds ~3 stages in flight per SM (two more are being converted): 78 KB x 148 SMs could not cover the HBM
-    // latency under load (ncu r02v: 3.0 TB/s, the converters starved 23 % of the time), so the same lanes also ask L2
-    // for the spills of step st + WG_PF (fire-and-forget bulk prefetch): the ring then streams from L2. =====
+    // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lanes 1..: one record field each) =====
     const float* rec_t = p.rec + (size_t)task * p.rec_task_stride;
-    auto src_of = [&](const WgStep& w, int ln, uint32_t& bytes) -> const float* {
+    for (int st = 0; st < nsteps; ++st) {
+      const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
+      const int stage = (int)((unsigned)st % (unsigned)WG_NS);
       const int CP = w.jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP, p0 = w.qq * npts;
       const int NF = w.jk == JET_V ? 2 : (w.jk == JET_G ? 4 : 5);
       const int NFT = NF + (p.hvp_records ? (w.jk == JET_V ? 1 : (w.jk == JET_G ? 3 : 4)) : 0);
-      if (ln == 0) {
-        bytes = (uint32_t)G::RAWZ;
-        const float* zsrc = w.zd ? p.zspd : p.zsp;
-        return zsrc + (size_t)task * p.zsp_task_stride + ((size_t)w.t * (L - 1) + (l - 1)) * p.tile_rows * W + (size_t)w.qq * WG_QR * W;
-      }
-      const int f = wg_raw_field_src(w.jk, w.tan, ln - 1);
-      bytes = (uint32_t)npts * 512u;
-      return rec_t + p.rec_seg_base[w.s] + ((size_t)w.tile * L + (l - 1)) * (size_t)(NFT * PTS) * W + (size_t)f * PTS * W +
-             (size_t)kt * PTS * 128 + (size_t)p0 * 128;
-    };
-    constexpr int WG_PF = 12;
-    for (int st = 0; st < nsteps; ++st) {
-      if (st == 0) {                                       // warm-up: the first WG_PF steps
-        for (int a = 1; a < WG_PF && a < nsteps; ++a) {
-          const WgStep wa = wg_decode_step(p, st0 + a, qpt_log2, npair_log2);
-          if (lane <= wg_raw_fields(wa.jk, wa.tan)) { uint32_t b; const float* sp = src_of(wa, lane, b); bulk_prefetch_l2(sp, b); }
-        }
-      }
-      if (st + WG_PF < nsteps) {
-        const WgStep wa = wg_decode_step(p, st0 + st + WG_PF, qpt_log2, npair_log2);
-        if (lane <= wg_raw_fields(wa.jk, wa.tan)) { uint32_t b; const float* sp = src_of(wa, lane, b); bulk_prefetch_l2(sp, b); }
-      }
-      const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
-      const int stage = (int)((unsigned)st % (unsigned)WG_NS);
       const int nfl = wg_raw_fields(w.jk, w.tan);
-      uint32_t fbytes = 0;
-      { uint32_t b; (void)src_of(w, 1, b); fbytes = b; }
+      const uint32_t fbytes = (uint32_t)npts * 512u;
       if (st >= WG_NS) mbar_wait(&raw_empty[stage], ((st / WG_NS) - 1) & 1);
       uint8_t* dst = raw + (size_t)stage * G::RAW;
       if (lane == 0) mbar_arrive_expect_tx(&raw_full[stage], (uint32_t)G::RAWZ + (uint32_t)nfl * fbytes);
       __syncwarp();
-      if (lane <= nfl) {
-        uint32_t b;
-        const float* sp = src_of(w, lane, b);
-        bulk_g2s(lane == 0 ? dst : dst + G::RAWZ + (size_t)(lane - 1) * fbytes, sp, b, &raw_full[stage]);
+      if (lane == 0) {
+        const float* zsrc = w.zd ? p.zspd : p.zsp;
+        const float* zq = zsrc + (size_t)task * p.zsp_task_stride + ((size_t)w.t * (L - 1) + (l - 1)) * p.tile_rows * W +
+                          (size_t)w.qq * WG_QR * W;
+        bulk_g2s(dst, zq, (uint32_t)G::RAWZ, &raw_full[stage]);
+      } else if (lane <= nfl) {
+        const int slot = lane - 1, f = wg_raw_field_src(w.jk, w.tan, slot);
+        const float* src = rec_t + p.rec_seg_base[w.s] + ((size_t)w.tile * L + (l - 1)) * (size_t)(NFT * PTS) * W +
+                           (size_t)f * PTS * W + (size_t)kt * PTS * 128 + (size_t)p0 * 128;
+        bulk_g2s(dst + G::RAWZ + (size_t)slot * fbytes, src, fbytes, &raw_full[stage]);
       }
     }
   }
