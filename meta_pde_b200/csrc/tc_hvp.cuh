@@ -231,8 +231,7 @@ struct HvTile {
     float* red = cx.red(ts);
     uint32_t* cmx = cx.cmax(ts, grp);
     uint64_t* dfull = cx.dfull + ts;
-    float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W +
-             (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
+    float* recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NFT * PTS) * W;   // see rec_off
     const int pg0 = grp * PG;                           // first point of this group
 
     if (ph == 0) {
@@ -254,9 +253,9 @@ struct HvTile {
           jet_act_fwd<JK>(om, z, a, sv);
           jet_act_tan<JK>(om, sv, zd, ad);
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
+          for (int f = 0; f < NF; ++f) recp[rec_off(NFT, PTS, 16 / CP, f, pl, n)] = sv[f];
           MPDE_UNROLL
-          for (int c = 0; c < C; ++c) recp[(size_t)((NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
+          for (int c = 0; c < C; ++c) recp[rec_off(NFT, PTS, 16 / CP, NF + c, pl, n)] = zd[c];
           park_point(o, od, q, a, ad, mx);
         }
         tmem_st8(tp + ch * TCH, o); tmem_st8(tt + ch * TCH, od);
@@ -299,9 +298,9 @@ struct HvTile {
           jet_act_fwd<JK>(om, z, a, sv);
           jet_act_tan<JK>(om, sv, zd, ad);
           MPDE_UNROLL
-          for (int f = 0; f < NF; ++f) recp[(size_t)((l * NFT + f)) * (PTS * W) + (pl) * 128] = sv[f];
+          for (int f = 0; f < NF; ++f) recp[(size_t)l * NFT * (PTS * W) + rec_off(NFT, PTS, 16 / CP, f, pl, n)] = sv[f];
           MPDE_UNROLL
-          for (int c = 0; c < C; ++c) recp[(size_t)((l * NFT + NF + c)) * (PTS * W) + (pl) * 128] = zd[c];
+          for (int c = 0; c < C; ++c) recp[(size_t)l * NFT * (PTS * W) + rec_off(NFT, PTS, 16 / CP, NF + c, pl, n)] = zd[c];
           park_point(o, od, q, a, ad, mx);
         }
         tmem_st8(tp + ch * TCH, o); tmem_st8(tt + ch * TCH, od);
@@ -434,14 +433,14 @@ struct HvTile {
         if (wg) psg[ps_off_wl(W, L) + W * OUT + tid] += g;
       }
     }
-    const float* rl = recp + (size_t)l * NFT * (PTS * W);   // this layer's records: [field][k tile][point][128]
+    const float* rl = recp + (size_t)l * NFT * (PTS * W);   // this layer's record block (layout: rec_off)
     float zs[4] = {0.f, 0.f, 0.f, 0.f}, zs1[4] = {0.f, 0.f, 0.f, 0.f};
     // the first chunk's record loads are issued before the accumulator wait (they do not depend on it)
     float svb[PPC][NF + C];
     MPDE_UNROLL
     for (int q = 0; q < PPC; ++q)
       MPDE_UNROLL
-      for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[f * (PTS * W) + (pg0 + q) * 128];
+      for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[rec_off(NFT, PTS, 16 / CP, f, pg0 + q, n)];
     if (!LAST) {
       int shz[8];
       prev_shifts<false>(cmx, seq, wshift_d[l + 1] - wshift[l + 1], shz);
@@ -493,7 +492,7 @@ struct HvTile {
         for (int c = 0; c < C; ++c) zd[c] = svb[q][NF + c];
         // this slot's record of the NEXT chunk: in flight while the chunk is processed
         MPDE_UNROLL
-        for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[f * (PTS * W) + (pg0 + chn * PPC + q) * 128];
+        for (int f = 0; f < NF + C; ++f) svb[q][f] = rl[rec_off(NFT, PTS, 16 / CP, f, pg0 + chn * PPC + q, n)];
         jet_act_bwd<JK>(om, sv, ab, zb);
         jet_act_bwd_tan<JK>(om, sv, zd, ab, abd, zbd);
         bsum += zb[0]; bsumd += zbd[0];

@@ -343,8 +343,7 @@ struct TcTile {
     // activation records of this tile: [layer][field][point][neuron]
     float* recp = nullptr;
     if (MODE != MODE_LOSS)
-      recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NF * PTS) * W +
-             (size_t)(n >> 7) * (PTS * 128) + (n & 127);   // record layout [layer][field][k tile][point][128 neurons]
+      recp = p.rec + (size_t)task * p.rec_task_stride + p.rec_seg_base[seg_id] + (size_t)tile * L * (NF * PTS) * W;   // see rec_off
 
     if (ph == 0) {
       // ---- layer 0 (in_dim = 2): direct ----
@@ -364,7 +363,7 @@ struct TcTile {
           jet_act_fwd<JK>(om, z, a, sv);
           if (MODE != MODE_LOSS) {
             MPDE_UNROLL
-            for (int f = 0; f < NF; ++f) recp[(size_t)(f) * (PTS * W) + (pl) * 128] = sv[f];
+            for (int f = 0; f < NF; ++f) recp[rec_off(NF, PTS, 16 / CP, f, pl, n)] = sv[f];
           }
           park_point(o, q, a, mx);
         }
@@ -401,7 +400,7 @@ struct TcTile {
           jet_act_fwd<JK>(om, z, a, sv);
           if (MODE != MODE_LOSS) {
             MPDE_UNROLL
-            for (int f = 0; f < NF; ++f) recp[(size_t)((l * NF + f)) * (PTS * W) + (pl) * 128] = sv[f];
+            for (int f = 0; f < NF; ++f) recp[(size_t)l * NF * (PTS * W) + rec_off(NF, PTS, 16 / CP, f, pl, n)] = sv[f];
           }
           park_point(o, q, a, mx);
         }
@@ -529,14 +528,14 @@ struct TcTile {
         ps[ps_off_wl(W, L) + W * OUT + tid] += g;
       }
     }
-    const float* rl = recp + (size_t)l * NF * (PTS * W);       // this layer's records: [field][k tile][point][128]
+    const float* rl = recp + (size_t)l * NF * (PTS * W);       // this layer's record block (layout: rec_off)
     float zs[4] = {0.f, 0.f, 0.f, 0.f};
     // the first batch of record loads is issued before the accumulator wait (it does not depend on it)
     float svb[SB][NF];
     MPDE_UNROLL
     for (int qq = 0; qq < SB; ++qq)
       MPDE_UNROLL
-      for (int f = 0; f < NF; ++f) svb[qq][f] = rl[f * (PTS * W) + qq * 128];
+      for (int f = 0; f < NF; ++f) svb[qq][f] = rl[rec_off(NF, PTS, 16 / CP, f, qq, n)];
     if (!LAST) {
       int shz[4];
       prev_shifts<false>(cmx, seq, shz);
@@ -577,7 +576,7 @@ struct TcTile {
         for (int f = 0; f < NF; ++f) sv[f] = svb[q][f];
         // this slot's record of the NEXT chunk: in flight while the chunk is processed
         MPDE_UNROLL
-        for (int f = 0; f < NF; ++f) svb[q][f] = rl[f * (PTS * W) + (chn * PPC + q) * 128];
+        for (int f = 0; f < NF; ++f) svb[q][f] = rl[rec_off(NF, PTS, 16 / CP, f, chn * PPC + q, n)];
         jet_act_bwd<JK>(om, sv, ab, zb);
         bsum += zb[0];
         if (LAST) {

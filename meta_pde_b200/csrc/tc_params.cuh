@@ -27,6 +27,14 @@ struct TcParams {
 MPDE_HD int ps_off_bias(int W, int l) { return 2 * W + l * W; }                  // l = 0..L-1
 MPDE_HD int ps_off_wl(int W, int L) { return (L + 2) * W; }
 MPDE_HD int ps_count(int W, int L, int OUT) { return (L + 2) * W + W * OUT + OUT; }
+// Record block of one (tile, layer), round-2 layout: [k tile][step of 16 jet rows][field][point of the step][128 neurons]
+// (PPS = points per 16-row step: 4 jet points or 16 value points), so that everything tc_wgrad_kernel needs for one
+// pipeline step of one k tile -- a range of fields of the step's points -- is ONE contiguous piece (it was one 2 KB piece
+// per field).  Offset (floats) of (field f, point pl) of neuron n; NFX = fields per point, PTS = points per tile.
+MPDE_HD size_t rec_off(int NFX, int PTS, int PPS, int f, int pl, int n) {
+  return (size_t)(n >> 7) * (size_t)(NFX * PTS * 128) + ((size_t)(pl / PPS) * NFX + f) * (size_t)(PPS * 128) +
+         (size_t)(pl % PPS) * 128 + (size_t)(n & 127);
+}
 // floats of activation records per (tile, layer): NF * PTS * W
 // (GRAD tiles: 64 rows = 16 jet points or 64 value points)
 MPDE_HD int rec_fields_points(int jk) { return jk == JET_V ? 2 * 64 : (jk == JET_G ? 4 * 16 : 5 * 16); }

@@ -7,8 +7,8 @@
 // kernel is the contraction over rows, and it is bound by reading those spills once from HBM.  One CTA per
 // (task, layer, 128-wide k tile) walks the task's rows in steps of 16:
 //   * a producer warp streams the raw fp32 spills of a step (16 rows of zbar: one contiguous bulk copy; the record
-//     fields of the step's points: one contiguous bulk copy per field, records are laid out
-//     [layer][field][k tile][point][128 neurons]) into a 3-stage shared-memory ring (cp.async.bulk + mbarrier): the
+//     fields of the step's points: ONE contiguous bulk copy, records are laid out
+//     [layer][k tile][step][field][point][128 neurons], rec_off in tc_params.cuh) into a 3/5-stage shared-memory ring (cp.async.bulk + mbarrier): the
 //     memory latency is hidden by the ring, not by registers;
 //   * two groups of 8 converter warps alternate steps: read the raw stage (conflict-free LDS), recompute h (hdot)
 //     from the records, split both operands into tf32 hi/lo (round-to-nearest, x = hi + lo) and write them K-major
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
     for (int st = 0; st < nsteps; ++st) {
       const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
       const int stage = (int)((unsigned)st % (unsigned)WG_NS);
-      const int CP = w.jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP, p0 = w.qq * npts;
+      const int CP = w.jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP;
       const int NF = w.jk == JET_V ? 2 : (w.jk == JET_G ? 4 : 5);
       const int NFT = NF + (p.hvp_records ? (w.jk == JET_V ? 1 : (w.jk == JET_G ? 3 : 4)) : 0);
       const int nfl = wg_raw_fields(w.jk, w.tan);
@@ -295,11 +295,13 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
         const float* zq = zsrc + (size_t)task * p.zsp_task_stride + ((size_t)w.t * (L - 1) + (l - 1)) * p.tile_rows * W +
                           (size_t)w.qq * WG_QR * W;
         bulk_g2s(dst, zq, (uint32_t)G::RAWZ, &raw_full[stage]);
-      } else if (lane <= nfl) {
-        const int slot = lane - 1, f = wg_raw_field_src(w.jk, w.tan, slot);
+      } else if (lane == 1) {
+        // the step's record fields of this k tile are one contiguous piece (rec_off in tc_params.cuh): fields
+        // f0 .. f0 + nfl - 1 of the step's points, [field][point][128 neurons]
+        const int f0 = wg_raw_field_src(w.jk, w.tan, 0);
         const float* src = rec_t + p.rec_seg_base[w.s] + ((size_t)w.tile * L + (l - 1)) * (size_t)(NFT * PTS) * W +
-                           (size_t)f * PTS * W + (size_t)kt * PTS * 128 + (size_t)p0 * 128;
-        bulk_g2s(dst + G::RAWZ + (size_t)slot * fbytes, src, fbytes, &raw_full[stage]);
+                           (size_t)kt * (size_t)(NFT * PTS * 128) + ((size_t)w.qq * NFT + f0) * (size_t)(npts * 128);
+        bulk_g2s(dst + G::RAWZ, src, (uint32_t)nfl * fbytes, &raw_full[stage]);
       }
     }
   }
