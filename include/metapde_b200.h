@@ -52,7 +52,8 @@ enum mpde_status {
   MPDE_INVALID_ARG = 1,        /* null pointer, non-positive size, bad enum           */
   MPDE_UNSUPPORTED_NET = 2,    /* width not in {32,64,128,256}, in_dim != 2, out_dim mismatch, non-SIREN */
   MPDE_WORKSPACE_TOO_SMALL = 3,
-  MPDE_CUDA_ERROR = 4
+  MPDE_CUDA_ERROR = 4,
+  MPDE_STATIC_SCRATCH_EXCEEDED = 5   /* mpde_field_eval_static: the problem needs more than MPDE_STATIC_SCRATCH_BYTES */
 };
 
 enum mpde_pde_kind { MPDE_PDE_POISSON = 0, MPDE_PDE_TD_BURGERS = 1, MPDE_PDE_HYPER_ELASTICITY = 2 };
@@ -125,6 +126,20 @@ size_t mpde_field_eval_workspace_bytes(const mpde_net_desc* net, int T);
 int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t theta_task_stride,
                     const float* coords, int64_t coords_task_stride, int n, float* out, void* workspace,
                     size_t workspace_bytes, void* stream);
+
+/* ---- K1f without allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ *   that cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *   Same arguments and results as mpde_field_eval, minus the workspace: the scratch (theta-hat + per-CTA partial terms,
+ *   mpde_field_eval_workspace_bytes) lives in a file-scope `static __device__` array of MPDE_STATIC_SCRATCH_BYTES (8 MiB)
+ *   that every GPU loading the library holds until the process exits.  Calls no cudaMalloc / cudaFree / allocating routine.
+ *   Limit: mpde_field_eval_workspace_bytes(net, T) <= MPDE_STATIC_SCRATCH_BYTES (about 60 tasks of a 3x64 field, 3 of a
+ *   5x256 one), otherwise MPDE_STATIC_SCRATCH_EXCEEDED.  All calls on a device SHARE the array: calls that may overlap on
+ *   the GPU (different streams, concurrent graph launches) race on it -- serialise them or use mpde_field_eval.  Nothing in
+ *   the array needs clearing between calls (every entry read by a call is written by it first). */
+#define MPDE_STATIC_SCRATCH_BYTES (8u << 20)
+size_t mpde_static_scratch_bytes(void);
+int mpde_field_eval_static(const mpde_net_desc* net, int T, const float* theta, int64_t theta_task_stride,
+                           const float* coords, int64_t coords_task_stride, int n, float* out, void* stream);
 
 /* ---- K4: parameter-sized fused ops ---------------------------------------
  * maml_inner_step after the gradient (src/nets/maml.py:72-96):

@@ -72,6 +72,8 @@ SIGNATURES = {
     "mpde_field_eval_workspace_bytes": (C.c_size_t, [C.POINTER(NetDesc), C.c_int]),
     "mpde_field_eval": (C.c_int, [C.POINTER(NetDesc), C.c_int, _P, C.c_int64, _P, C.c_int64, C.c_int, _P, _P,
                                   C.c_size_t, _P]),
+    "mpde_static_scratch_bytes": (C.c_size_t, []),
+    "mpde_field_eval_static": (C.c_int, [C.POINTER(NetDesc), C.c_int, _P, C.c_int64, _P, C.c_int64, C.c_int, _P, _P]),
     "mpde_maml_inner_update": (C.c_int, [C.c_int, C.c_int, _P, C.c_int64, _P, _P, C.c_float, C.c_int, C.c_float,
                                          C.c_float, _P, _P, _P]),
     "mpde_sumsq": (C.c_int, [_P, C.c_int64, _P, _P, C.c_size_t, _P]),
@@ -142,7 +144,7 @@ class Kernels:
             # every ABI entry point is called with this object's device current: the library sets per-device kernel
             # attributes and launches on the caller's stream, which must belong to the current device
             pure = ("mpde_param_count", "mpde_num_point_sets", "mpde_num_terms", "mpde_num_pde_params", "mpde_status_string",
-                    "mpde_launch_count", "mpde_backend", "mpde_prof_enable", "mpde_sumsq_workspace_bytes")
+                    "mpde_launch_count", "mpde_backend", "mpde_prof_enable", "mpde_sumsq_workspace_bytes", "mpde_static_scratch_bytes")
             for name in SIGNATURES:
                 if name not in pure:       # includes the *_workspace_bytes planners: they query the current device
                     setattr(self, "_" + name, self._guarded(getattr(abi, name)))

@@ -467,6 +467,7 @@ const char* mpde_status_string(int s) {
     case MPDE_UNSUPPORTED_NET: return "unsupported network (SIREN, in_dim 2, layer_size in {32,64,128,256}, out_dim matching the PDE)";
     case MPDE_WORKSPACE_TOO_SMALL: return "workspace too small";
     case MPDE_CUDA_ERROR: return "CUDA error";
+    case MPDE_STATIC_SCRATCH_EXCEEDED: return "problem needs more scratch than the library's static device array holds (mpde_static_scratch_bytes): use the workspace entry point";
   }
   return "unknown status";
 }
@@ -586,6 +587,54 @@ int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t
   kp.want_grad = 0;
   int G = tiles < 4096 ? tiles : 4096;
   return dispatch(W, kpde, MODE_LOSS, 1, &kp, G, T, stream, nullptr);
+}
+
+// ------------------------------------------------------------------ K1f without any allocation
+// mpde_field_eval with its scratch (theta-hat + per-CTA partial terms) in a file-scope device array instead of a caller
+// workspace: for callers that cannot allocate (CUDA-graph capture, serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds the array until the process exits.
+#ifndef MPDE_EMU
+static __device__ __align__(256) unsigned char g_static_scratch[MPDE_STATIC_SCRATCH_BYTES];
+static void* g_static_scratch_ptr[PerDeviceOnce::MAXDEV];   // DEVICE address of the array, per device (the symbol's name is
+                                                            // only a host-side stand-in: never pass it to a kernel)
+static int static_scratch_address(void** out) {
+  static PerDeviceOnce once;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= PerDeviceOnce::MAXDEV) return MPDE_CUDA_ERROR;
+  const cudaError_t e = once.run([&]() {          // once per device, with that device current
+    void* ptr = nullptr;
+    const cudaError_t ee = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (ee == cudaSuccess) g_static_scratch_ptr[dev] = ptr;
+    return ee;
+  });
+  if (e != cudaSuccess || g_static_scratch_ptr[dev] == nullptr) return MPDE_CUDA_ERROR;
+  *out = g_static_scratch_ptr[dev];
+  return MPDE_OK;
+}
+#endif
+
+size_t mpde_static_scratch_bytes(void) { return (size_t)MPDE_STATIC_SCRATCH_BYTES; }
+
+int mpde_field_eval_static(const mpde_net_desc* net, int T, const float* theta, int64_t theta_task_stride,
+                           const float* coords, int64_t coords_task_stride, int n, float* out, void* stream) {
+#ifdef MPDE_EMU
+  (void)net; (void)T; (void)theta; (void)theta_task_stride; (void)coords; (void)coords_task_stride; (void)n; (void)out; (void)stream;
+  return MPDE_INVALID_ARG;      // the emulator build has no device memory
+#else
+  int rc = check_net(net, 0);
+  if (rc) return rc;
+  if (!theta || !coords || !out || T < 1 || n < 1) return MPDE_INVALID_ARG;
+  const size_t need = mpde_field_eval_workspace_bytes(net, T);
+  if (need == 0) return MPDE_UNSUPPORTED_NET;
+  if (need > (size_t)MPDE_STATIC_SCRATCH_BYTES) return MPDE_STATIC_SCRATCH_EXCEEDED;
+  void* scratch = nullptr;
+  rc = static_scratch_address(&scratch);
+  if (rc) return rc;
+  // nothing in the scratch has to start at zero: prep_kernel writes every theta-hat entry the jet kernel reads and the
+  // kernel writes (never accumulates) its per-CTA partial terms, so the previous call's contents are simply overwritten
+  return mpde_field_eval(net, T, theta, theta_task_stride, coords, coords_task_stride, n, out, scratch,
+                         (size_t)MPDE_STATIC_SCRATCH_BYTES, stream);
+#endif
 }
 
 // ------------------------------------------------------------------ K4
