@@ -9,7 +9,7 @@ jax 0.2.20 derivations on top of it (``split``: counts iota(2n); ``_random_bits`
 zero-padded, the counter array split in two halves; ``uniform``: mantissa trick on bits >> 9).
 
 Pinned by the only golden vectors the reference holds for anything near the path
-(``src/.ipynb_checkpoints/Untitled-checkpoint.ipynb:183,215,236,257-259``): see tests/test_compat_random.py.
+(``src/.ipynb_checkpoints/Untitled-checkpoint.ipynb:183,215,236,257-259``): see tests/test_compat_host.py::test_prng_golden_vectors (and tests/test_sampler_parity.py for the samplers built on it).
 Sampling is host-side plumbing: the kernels consume its output.
 """
 import numpy as np

@@ -355,6 +355,12 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     for (int s = 0; s < MAX_SEG; ++s) tp.rec_seg_base[s] = (s < pl.n_seg) ? pl.rec_seg_base[s] : 0;
     tp.zsp = zsp; tp.zsp_task_stride = pl.zsp_per_task;
     tp.psmall = psmall; tp.PS = pl.PS;
+    {
+      // off by default since round 2: with two units in flight per SM the prefetched lines were evicted before the reverse
+      // pass read them (DRAM reads of the HVP launch 77 -> 124 GB, +2.5..4 % time); MPDE_REC_PREFETCH=1 re-enables it
+      static const int pf = []() { const char* e = getenv("MPDE_REC_PREFETCH"); return (e && e[0] == '1') ? 1 : 0; }();
+      tp.rec_prefetch = pf;
+    }
     if (mode == MODE_HVP) {
       tc::HvParams hp;
       hp.t = tp;

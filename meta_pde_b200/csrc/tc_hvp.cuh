@@ -734,7 +734,7 @@ __global__ void __launch_bounds__(HvGeo<W>::NT, 1) tc_hvp_kernel(const __grid_co
           for (int ts = 0; ts < nts; ++ts) {
             if (ts) { mbar_wait(&cx.xready[1], xpar1); xpar1 ^= 1u; } else { mbar_wait(&cx.xready[0], xpar0); xpar0 ^= 1u; }
             const int l = 2 * L - 2 - step;                // step L + j (j = 0 .. L-2) -> layer L-2-j
-            if (step >= L && l >= 0) {
+            if (p.rec_prefetch && step >= L && l >= 0) {
               const int t = bx + (i0 + ts) * gx;
               int sgi = 0;
               while (sgi + 1 < kp.n_seg && t >= kp.seg_tile_begin[sgi + 1]) ++sgi;

@@ -809,7 +809,7 @@ __global__ void __launch_bounds__(TcGeo<W>::NT, 1) tc_pde_kernel(const __grid_co
           for (int pr = 0; pr < npair; ++pr) {
             if (pr) { mbar_wait(&cx.xready[1], xpar1); xpar1 ^= 1u; } else { mbar_wait(&cx.xready[0], xpar0); xpar0 ^= 1u; }
             const int l = 2 * L - 2 - step;                // step L + j (j = 0 .. L-2) -> layer L-2-j
-            if (step >= L && l >= 0) {
+            if (p.rec_prefetch && step >= L && l >= 0) {
               for (int g = 0; g < NSLOT; ++g) {
                 if (i0 + pr * NSLOT + g >= n_mine) break;
                 const int t = bx + (i0 + pr * NSLOT + g) * gx;

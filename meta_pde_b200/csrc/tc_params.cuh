@@ -21,6 +21,7 @@ struct TcParams {
   long long zsp_task_stride;       // floats
   float* psmall;                   // [T][G][PS] per-CTA partials of the small parameters (first/last layer, biases)
   int PS;
+  int rec_prefetch;                // the record-prefetch warp asks L2 for the next reverse layer's records (MPDE_REC_PREFETCH=1; off by default)
 };
 
 // per-CTA partial layout of the small parameters: w0 [2][W], b0 [W], b_l [W] (l = 1..L-1), wL [W][OUT], bL [OUT]
