@@ -215,8 +215,14 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
     };
     int done_gen = 0;                                   // generations 0 .. done_gen-1 are in the master copy
     const float om = p.omega;
+    int cseg = 0;
     for (int st = grp; st < nsteps; st += G::NGRP) {
-      const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
+      // segment look-up is monotonic in st: no full decode per step
+      const int t_st = (st0 + st) >> (qpt_log2 + npair_log2);
+      while (cseg + 1 < p.n_seg && t_st >= p.seg_tile_begin[cseg + 1]) ++cseg;
+      WgStep w;
+      w.jk = p.seg_jk[cseg];
+      w.tan = HV && (((st0 + st) & 1) == 0);               // HV: steps alternate (hdot, zbar) / (h, zbardot)
       // promotion lags the MMAs by two steps (no pipeline drain at a generation boundary)
       while (st >= 2 && done_gen < (st - 2) / WG_GROUP) promote(done_gen++);
       const int stage = (int)((unsigned)st % (unsigned)WG_NS);
@@ -276,32 +282,45 @@ __global__ void __launch_bounds__(WgGeo<W, HV>::NT, 1) tc_wgrad_kernel(const __g
       __syncwarp();
     }
   } else {
-    // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lanes 1..: one record field each) =====
+    // ===== producer: raw spills of step st -> stage st % WG_NS (lane 0: zbar rows, lane 1: the step's record fields).
+    // Everything that only changes per tile is computed per tile and the per-step work is a handful of adds: round 2's
+    // profile showed this ONE warp busy 100 % of the time (a full step decode, 64-bit multiplies and a modulo per step)
+    // while the 16 converter warps waited for data 19 % of theirs -- the producer's instruction stream paced the kernel. =====
     const float* rec_t = p.rec + (size_t)task * p.rec_task_stride;
-    for (int st = 0; st < nsteps; ++st) {
-      const WgStep w = wg_decode_step(p, st0 + st, qpt_log2, npair_log2);
-      const int stage = (int)((unsigned)st % (unsigned)WG_NS);
-      const int CP = w.jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP;
-      const int NF = w.jk == JET_V ? 2 : (w.jk == JET_G ? 4 : 5);
-      const int NFT = NF + (p.hvp_records ? (w.jk == JET_V ? 1 : (w.jk == JET_G ? 3 : 4)) : 0);
-      const int nfl = wg_raw_fields(w.jk, w.tan);
+    const float* zp_t = p.zsp + (size_t)task * p.zsp_task_stride;
+    const float* zd_t = p.want_hv ? p.zspd + (size_t)task * p.zsp_task_stride : zp_t;
+    int seg = 0;
+    uint32_t stage = 0, ephase = 1;                      // ring stage of the next step; parity to wait on raw_empty with
+    int st = 0;
+    for (int t = t_lo; t < t_hi; ++t) {
+      while (seg + 1 < p.n_seg && t >= p.seg_tile_begin[seg + 1]) ++seg;
+      const int jk = p.seg_jk[seg], tile = t - p.seg_tile_begin[seg];
+      const int CP = jk == JET_V ? 1 : 4, PTS = p.tile_rows / CP, npts = WG_QR / CP;
+      const int NF = jk == JET_V ? 2 : (jk == JET_G ? 4 : 5);
+      const int NFT = NF + (p.hvp_records ? (jk == JET_V ? 1 : (jk == JET_G ? 3 : 4)) : 0);
       const uint32_t fbytes = (uint32_t)npts * 512u;
-      if (st >= WG_NS) mbar_wait(&raw_empty[stage], ((st / WG_NS) - 1) & 1);
-      uint8_t* dst = raw + (size_t)stage * G::RAW;
-      if (lane == 0) mbar_arrive_expect_tx(&raw_full[stage], (uint32_t)G::RAWZ + (uint32_t)nfl * fbytes);
-      __syncwarp();
-      if (lane == 0) {
-        const float* zsrc = w.zd ? p.zspd : p.zsp;
-        const float* zq = zsrc + (size_t)task * p.zsp_task_stride + ((size_t)w.t * (L - 1) + (l - 1)) * p.tile_rows * W +
-                          (size_t)w.qq * WG_QR * W;
-        bulk_g2s(dst, zq, (uint32_t)G::RAWZ, &raw_full[stage]);
-      } else if (lane == 1) {
-        // the step's record fields of this k tile are one contiguous piece (rec_off in tc_params.cuh): fields
-        // f0 .. f0 + nfl - 1 of the step's points, [field][point][128 neurons]
-        const int f0 = wg_raw_field_src(w.jk, w.tan, 0);
-        const float* src = rec_t + p.rec_seg_base[w.s] + ((size_t)w.tile * L + (l - 1)) * (size_t)(NFT * PTS) * W +
-                           (size_t)kt * (size_t)(NFT * PTS * 128) + ((size_t)w.qq * NFT + f0) * (size_t)(npts * 128);
-        bulk_g2s(dst + G::RAWZ, src, (uint32_t)nfl * fbytes, &raw_full[stage]);
+      // this tile's zbar rows of layer l and record block of layer l - 1, k tile kt
+      const size_t zoff = ((size_t)t * (L - 1) + (l - 1)) * (size_t)p.tile_rows * W;
+      const float* rec_blk = rec_t + p.rec_seg_base[seg] + ((size_t)tile * L + (l - 1)) * (size_t)(NFT * PTS) * W +
+                             (size_t)kt * (size_t)(NFT * PTS * 128);
+      const int step_floats = NFT * npts * 128;          // records of one 16-row step
+      // per pair (0: (hdot, zbar) / gradient (h, zbar); 1: (h, zbardot)): fields and their first field
+      const int nfl0 = wg_raw_fields(jk, p.want_hv != 0), f00 = wg_raw_field_src(jk, p.want_hv != 0, 0);
+      const int nfl1 = wg_raw_fields(jk, false), f01 = wg_raw_field_src(jk, false, 0);
+      for (int qq = 0; qq < qpt; ++qq) {
+        for (int pair = 0; pair < npair; ++pair, ++st) {
+          const int nfl = pair ? nfl1 : nfl0, f0 = pair ? f01 : f00;
+          if (st >= WG_NS) mbar_wait(&raw_empty[stage], ephase);
+          uint8_t* dst = raw + (size_t)stage * G::RAW;
+          const uint32_t rbytes = (uint32_t)nfl * fbytes;
+          if (lane == 0) {
+            mbar_arrive_expect_tx(&raw_full[stage], (uint32_t)G::RAWZ + rbytes);
+            bulk_g2s(dst, (pair ? zd_t : zp_t) + zoff + (size_t)qq * (WG_QR * W), (uint32_t)G::RAWZ, &raw_full[stage]);
+            // the step's record fields f0 .. f0 + nfl - 1 of this k tile are one contiguous piece (rec_off in tc_params.cuh)
+            bulk_g2s(dst + G::RAWZ, rec_blk + (size_t)qq * step_floats + (size_t)f0 * (npts * 128), rbytes, &raw_full[stage]);
+          }
+          if (++stage == (uint32_t)WG_NS) { stage = 0; if (st >= WG_NS - 1) ephase ^= 1u; }
+        }
       }
     }
   }
