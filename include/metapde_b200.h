@@ -127,6 +127,22 @@ int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t
                     const float* coords, int64_t coords_task_stride, int n, float* out, void* workspace,
                     size_t workspace_bytes, void* stream);
 
+/* ---- Samplers: jax.random on the GPU.  Replaces the jax.random calls inside the reference's point
+ *   samplers (src/poisson/poisson_common.py:69-119, src/burgers/td_burgers_common.py:117-186): jax 0.2.20's threefry2x32
+ *   `split` / `_random_bits` / `uniform`, bit-exact with meta_pde_b200/compat/random.py (pinned by the reference's jax.random
+ *   known answers).  keys: device uint32 [S][2], one key per sample; every output row s uses keys[s].
+ *   mpde_random_bits / _uniform: out [S][n] = random bits / uniform(keys[s], (n,), minval, maxval).
+ *   mpde_random_split: out [S][num][2] = split(keys[s], num).
+ *   mpde_sample_poisson_candidates: sample_points(keys[s], n, params) of poisson_common.py up to the final selection:
+ *     boundary [S][n][2] (final), cand_xy [S][3n][2] and cand_g [S][3n] = the candidates of sample_points_in_domain and their
+ *     Gumbel selection keys (+inf inside the hole); the domain points are the n candidates with the smallest cand_g, in
+ *     ascending (stable) order -- jax.random.choice(replace=False, p).  geo [S][2] = the task's geometry params (c1, c2). */
+int mpde_random_bits(int S, const uint32_t* keys, int64_t n, uint32_t* out, void* stream);
+int mpde_random_uniform(int S, const uint32_t* keys, int64_t n, float minval, float maxval, float* out, void* stream);
+int mpde_random_split(int S, const uint32_t* keys, int num, uint32_t* out, void* stream);
+int mpde_sample_poisson_candidates(int S, const uint32_t* keys, int n, const float* geo, float xmin, float xmax, float ymin,
+                                   float ymax, float* boundary, float* cand_xy, float* cand_g, void* stream);
+
 /* ---- K1f without allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
  *   that cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
  *   Same arguments and results as mpde_field_eval, minus the workspace: the scratch (theta-hat + per-CTA partial terms,

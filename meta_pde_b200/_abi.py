@@ -72,6 +72,10 @@ SIGNATURES = {
     "mpde_field_eval_workspace_bytes": (C.c_size_t, [C.POINTER(NetDesc), C.c_int]),
     "mpde_field_eval": (C.c_int, [C.POINTER(NetDesc), C.c_int, _P, C.c_int64, _P, C.c_int64, C.c_int, _P, _P,
                                   C.c_size_t, _P]),
+    "mpde_random_bits": (C.c_int, [C.c_int, _P, C.c_int64, _P, _P]),
+    "mpde_random_uniform": (C.c_int, [C.c_int, _P, C.c_int64, C.c_float, C.c_float, _P, _P]),
+    "mpde_random_split": (C.c_int, [C.c_int, _P, C.c_int, _P, _P]),
+    "mpde_sample_poisson_candidates": (C.c_int, [C.c_int, _P, C.c_int, _P, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, _P, _P]),
     "mpde_static_scratch_bytes": (C.c_size_t, []),
     "mpde_field_eval_static": (C.c_int, [C.POINTER(NetDesc), C.c_int, _P, C.c_int64, _P, C.c_int64, C.c_int, _P, _P]),
     "mpde_maml_inner_update": (C.c_int, [C.c_int, C.c_int, _P, C.c_int64, _P, _P, C.c_float, C.c_int, C.c_float,
@@ -336,6 +340,45 @@ class Kernels:
                                                     _ptr(self._t(a_t, "alpha")), a_s, int(softplus_lrs),
                                                     float(inner_lr), float(clip), _ptr(out), _ptr(gn), self._stream()))
         return out, gn
+
+    # ---------------------------------------------------------------- samplers (jax.random on the GPU)
+    def _keys(self, keys):
+        """[S, 2] uint32 key pairs (numpy / tensor) -> int32 device tensor holding the same bits"""
+        import numpy as _np
+        if not torch.is_tensor(keys):
+            keys = torch.from_numpy(_np.ascontiguousarray(_np.asarray(keys, dtype=_np.uint32).reshape(-1, 2)).view(_np.int32))
+        if keys.dtype != torch.int32 or keys.dim() != 2 or keys.shape[1] != 2:
+            raise MpdeError("keys: expected [S, 2] uint32 key pairs")
+        return keys.to(self.device).contiguous()
+
+    def random_bits(self, keys, n):
+        k = self._keys(keys)
+        out = torch.empty(k.shape[0], int(n), dtype=torch.int32, device=self.device)
+        self._check(self._fn("mpde_random_bits")(k.shape[0], _ptr(k), int(n), _ptr(out), self._stream()))
+        return out
+
+    def random_uniform(self, keys, n, minval=0.0, maxval=1.0):
+        k = self._keys(keys)
+        out = torch.empty(k.shape[0], int(n), dtype=torch.float32, device=self.device)
+        self._check(self._fn("mpde_random_uniform")(k.shape[0], _ptr(k), int(n), float(minval), float(maxval), _ptr(out), self._stream()))
+        return out
+
+    def random_split(self, keys, num):
+        k = self._keys(keys)
+        out = torch.empty(k.shape[0], int(num), 2, dtype=torch.int32, device=self.device)
+        self._check(self._fn("mpde_random_split")(k.shape[0], _ptr(k), int(num), _ptr(out), self._stream()))
+        return out
+
+    def sample_poisson_candidates(self, keys, n, geo, xmin, xmax, ymin, ymax):
+        k = self._keys(keys)
+        S, n = k.shape[0], int(n)
+        geo = self._t(torch.as_tensor(geo, dtype=torch.float32).to(self.device).reshape(S, 2).contiguous(), "geo")
+        boundary = torch.empty(S, n, 2, dtype=torch.float32, device=self.device)
+        cand_xy = torch.empty(S, 3 * n, 2, dtype=torch.float32, device=self.device)
+        cand_g = torch.empty(S, 3 * n, dtype=torch.float32, device=self.device)
+        self._check(self._fn("mpde_sample_poisson_candidates")(S, _ptr(k), n, _ptr(geo), float(xmin), float(xmax), float(ymin),
+                                                              float(ymax), _ptr(boundary), _ptr(cand_xy), _ptr(cand_g), self._stream()))
+        return boundary, cand_xy, cand_g
 
     def prof_enable(self, on=True):
         self._check(self.abi.mpde_prof_enable(int(bool(on))))

@@ -34,6 +34,7 @@ def define_common():
     _def("integer", "num_tsteps", 101, "number of time steps for td_burgers")
     _def("integer", "sample_tsteps", 64, "number of time steps for td_burgers")
     _def("boolean", "sample_time_random", True, "random time sample for NN")
+    _def("boolean", "gpu_samplers", False, "metapde_b200 only: draw the collocation points on the GPU (same keys, same points; poisson and td_burgers)")
     _def("float", "max_reynolds", 100, "Reynolds number scale")
     _def("string", "burgers_pde", "default", "types of burgers equation")
     _def("float", "xmin", 0.0, "")

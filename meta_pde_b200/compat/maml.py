@@ -162,31 +162,58 @@ def multi_task_grad_and_losses(maml_def, key, initial_model, inner_lrs=None, tas
     return grads, losses, (meta, aux)
 
 
+def _gpu_sampled_sets(pde, tasks, K, K_):
+    """All (2K + 2) x T point draws of one outer step on the GPU (compat/gpu_samplers.py; --gpu_samplers): the same keys the
+    host route hands to ``sample`` (maml.py:132-140,158,192), one launch per distinct point count.  None when this PDE has
+    no GPU sampler."""
+    import numpy as np
+    from . import gpu_samplers
+    T = len(tasks)
+    inner_keys, outer_keys = np.zeros((K + 1, T, 2), np.uint32), np.zeros((K + 1, T, 2), np.uint32)
+    for t, ((inner_fn, outer_fn), rollout_key, outer_loss_key) in enumerate(tasks):
+        k1s, k2s, final_key = _rollout_keys(rollout_key, K)
+        for k in range(K):
+            inner_keys[k, t], outer_keys[k, t] = k1s[k], k2s[k]
+        inner_keys[K, t], outer_keys[K, t] = final_key, outer_loss_key
+    (inner_fn0, outer_fn0) = tasks[0][0]
+    params = [fn[0].params for fn, _, _ in tasks] * (K + 1)
+    a = gpu_samplers.sample_points_batched(pde, inner_keys.reshape(-1, 2), inner_fn0.n_points, params, K_)
+    if a is None:
+        return None
+    b = gpu_samplers.sample_points_batched(pde, outer_keys.reshape(-1, 2), outer_fn0.n_points, params, K_)
+    split = lambda sets, k: [x.reshape(K + 1, T, *x.shape[1:])[k].contiguous() for x in sets]
+    return ([split(a, k) for k in range(K)], [split(b, k) for k in range(K)], split(a, K), split(b, K))
+
+
 def _fused_outer(maml_def, tasks, initial_model, inner_lrs, K, scale):
     dev = initial_model.theta.device
     K_ = ops.kernels(dev)
     inner_fn0, outer_fn0 = tasks[0][0]
     pde = inner_fn0.pde
     T = len(tasks)
-    inner_pts, outer_pts = [[] for _ in range(K)], [[] for _ in range(K)]
-    final_pts, aux_pts, prms = [], [], []
-    for (inner_fn, outer_fn), rollout_key, outer_loss_key in tasks:
-        k1s, k2s, final_key = _rollout_keys(rollout_key, K)
-        for k in range(K):
-            inner_pts[k].append(inner_fn.sample(k1s[k]))
-            outer_pts[k].append(outer_fn.sample(k2s[k]))
-        final_pts.append(inner_fn.sample(final_key))
-        aux_pts.append(outer_fn.sample(outer_loss_key))
-        prms.append(pde.abi_params(inner_fn.params))
+    prms = [pde.abi_params(inner_fn.params) for (inner_fn, _), _, _ in tasks]
+    sets = _gpu_sampled_sets(pde, tasks, K, K_) if FLAGS.gpu_samplers else None
+    if sets is None:
+        inner_pts, outer_pts = [[] for _ in range(K)], [[] for _ in range(K)]
+        final_pts, aux_pts = [], []
+        for (inner_fn, outer_fn), rollout_key, outer_loss_key in tasks:
+            k1s, k2s, final_key = _rollout_keys(rollout_key, K)
+            for k in range(K):
+                inner_pts[k].append(inner_fn.sample(k1s[k]))
+                outer_pts[k].append(outer_fn.sample(k2s[k]))
+            final_pts.append(inner_fn.sample(final_key))
+            aux_pts.append(outer_fn.sample(outer_loss_key))
+        sets = ([_stack_points(pde, p) for p in inner_pts], [_stack_points(pde, p) for p in outer_pts],
+                _stack_points(pde, final_pts), _stack_points(pde, aux_pts))
+    inner_sets, outer_sets, final_sets, aux_sets = sets
     prm = torch.stack(prms).to(dev).contiguous()
     lrs = inner_lrs.theta.contiguous() if inner_lrs is not None else None
     # one packed buffer [g_theta | g_lrs]: the layout of the all-reduce and of the fused outer step (mpde_outer_step)
     P = initial_model.theta.numel()
     packed = torch.empty((1 + (K if lrs is not None else 0)) * P, dtype=torch.float32, device=dev)
     out = K_.maml_outer(initial_model.net_desc(K_), pde.name, inner_fn0.bc_weight, _cfg(maml_def, K),
-                        initial_model.theta.detach().contiguous(), lrs, [_stack_points(pde, p) for p in inner_pts],
-                        [_stack_points(pde, p) for p in outer_pts], _stack_points(pde, final_pts),
-                        _stack_points(pde, aux_pts), prm, T, grad_scale=scale, out_g_theta=packed[:P],
+                        initial_model.theta.detach().contiguous(), lrs, inner_sets, outer_sets, final_sets, aux_sets,
+                        prm, T, grad_scale=scale, out_g_theta=packed[:P],
                         out_g_lrs=packed[P:].view(K, P) if lrs is not None else None)
     g_model = Model(initial_model.module, out["g_theta"])
     g_model.packed = packed

@@ -5,6 +5,7 @@
 #include "../../include/metapde_b200.h"
 #include "host_common.h"
 #include "aux_kernels.cuh"
+#include "sampler_kernels.cuh"
 #ifndef MPDE_EMU
 #include "tc_params.cuh"
 #endif
@@ -593,6 +594,31 @@ int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t
   kp.want_grad = 0;
   int G = tiles < 4096 ? tiles : 4096;
   return dispatch(W, kpde, MODE_LOSS, 1, &kp, G, T, stream, nullptr);
+}
+
+// ------------------------------------------------------------------ samplers: jax.random on the GPU
+int mpde_random_bits(int S, const uint32_t* keys, int64_t n, uint32_t* out, void* stream) {
+  if (S < 1 || n < 1 || !keys || !out) return MPDE_INVALID_ARG;
+  int gx = grid_for(n); if (gx > 1024) gx = 1024;
+  return launch_simple(random_bits_kernel, gx, S, 256, 0, stream, keys, (long long)n, out);
+}
+int mpde_random_uniform(int S, const uint32_t* keys, int64_t n, float minval, float maxval, float* out, void* stream) {
+  if (S < 1 || n < 1 || !keys || !out) return MPDE_INVALID_ARG;
+  int gx = grid_for(n); if (gx > 1024) gx = 1024;
+  return launch_simple(random_uniform_kernel, gx, S, 256, 0, stream, keys, (long long)n, minval, maxval, out);
+}
+int mpde_random_split(int S, const uint32_t* keys, int num, uint32_t* out, void* stream) {
+  if (S < 1 || num < 1 || !keys || !out) return MPDE_INVALID_ARG;
+  return launch_simple(random_split_kernel, S, 1, 32, 0, stream, keys, num, out);
+}
+int mpde_sample_poisson_candidates(int S, const uint32_t* keys, int n, const float* geo, float xmin, float xmax, float ymin,
+                                   float ymax, float* boundary, float* cand_xy, float* cand_g, void* stream) {
+  if (S < 1 || n < 1 || !keys || !geo || !boundary || !cand_xy || !cand_g) return MPDE_INVALID_ARG;
+  PoissonSampleParams p;
+  p.S = S; p.n = n; p.keys = keys; p.geo = geo; p.xmin = xmin; p.xmax = xmax; p.ymin = ymin; p.ymax = ymax;
+  p.boundary = boundary; p.cand_xy = cand_xy; p.cand_g = cand_g;
+  int gx = grid_for(4LL * n); if (gx > 256) gx = 256;
+  return launch_simple(poisson_sample_kernel, gx, S, 256, 0, stream, p);
 }
 
 // ------------------------------------------------------------------ K1f without any allocation

@@ -81,3 +81,13 @@ def test_leap_train_step_matches_oracle(emu_kernels, grad_clip):
 def test_finetune_train_step_matches_oracle(emu_kernels, grad_clip):
     errs, clipped = pc.check_finetune_train_steps(emu_kernels, "td_burgers", 32, 2, 70, T=2, steps=3, grad_clip=grad_clip)
     assert all(clipped) == (grad_clip < 1.0), clipped
+
+
+def test_gpu_sampler_kernels_on_the_emulator(emu_kernels):
+    """jax.random (threefry split / bits / uniform) and the batched Poisson / Burgers point samplers of
+    csrc/sampler_kernels.cuh, run through the emulator build: bit-exact integers and uniforms, same points as the host
+    samplers that tests/test_sampler_parity.py pins to the reference's sampler source."""
+    import sampler_cases as sc
+    sc.check_threefry(emu_kernels)
+    sc.check_poisson(emu_kernels)
+    sc.check_burgers(emu_kernels)

@@ -137,6 +137,32 @@ def test_drivers_run_with_reference_flag_strings(gpu_kernels, tmp_path):
     assert "step: 8" in open(tmp_path / "nn" / "t" / "log.txt").read()
 
 
+def test_gpu_samplers_match_host_samplers(gpu_kernels, flags_small):
+    """csrc/sampler_kernels.cuh through the C ABI: threefry bit-exact, Poisson / Burgers points = the host samplers' (which
+    are pinned to the reference's sampler source), and the fused MAML route gives the same meta-gradient with
+    --gpu_samplers as with the host samplers (same keys -> same points -> same numbers)."""
+    import sampler_cases as sc
+    sc.check_threefry(gpu_kernels)
+    sc.check_poisson(gpu_kernels, n=256, S=8)
+    sc.check_burgers(gpu_kernels)
+    pde = pdes.get_pde("poisson")
+    model = _model(pde)
+    T, Ksteps = 3, 2
+    lrs = field.Model(model.module, torch.ones(Ksteps, model.theta.numel(), device="cuda"))
+    mdef = maml.MamlDef(Momentum(learning_rate=1e-2, beta=0.0).create, tasks.make_task_loss_fns_factory(pde), Ksteps, T, True, 0.1)
+    saved = FLAGS.gpu_samplers
+    try:
+        FLAGS.gpu_samplers = False
+        (g0, l0), losses0, (meta0, _) = maml.multi_task_grad_and_losses(mdef, jr.PRNGKey(5), model, lrs)
+        FLAGS.gpu_samplers = True
+        (g1, l1), losses1, (meta1, _) = maml.multi_task_grad_and_losses(mdef, jr.PRNGKey(5), model, lrs)
+    finally:
+        FLAGS.gpu_samplers = saved
+    # boundary points differ by ~1e-7 (cos / sin), the drawn candidates are the same
+    assert rel_l2(g1.theta.cpu(), g0.theta.cpu()) < 1e-4 and rel_l2(l1.theta.cpu(), l0.theta.cpu()) < 1e-4
+    assert rel_l2(losses1.cpu(), losses0.cpu()) < 1e-5 and rel_l2(meta1.cpu(), meta0.cpu()) < 1e-5
+
+
 @pytest.mark.parametrize("name", ["poisson", "td_burgers"])
 def test_deployment_rollout_matches_oracle(gpu_kernels, flags_small, name):
     """get_final_model / make_coef_func / vmap_validation_error (src/maml_pde.py:163-201, trainer_util.py:501-575):
