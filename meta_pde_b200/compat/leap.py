@@ -105,19 +105,36 @@ def _fused(leap_def, od, tasks, initial_model, K, scale):
     dev = initial_model.theta.device
     K_ = ops.kernels(dev)
     pde = tasks[0][0].pde
-    loss0, step, new, prms = [], [[] for _ in range(K)], [[] for _ in range(K)], []
-    for fn, rollout_key in tasks:
-        loss0_key, inner_keys = _rollout_keys(rollout_key, K)
-        loss0.append(fn.sample(loss0_key))
-        for k in range(K):
-            k1, k2 = jr.split(inner_keys[k], 2)
-            step[k].append(fn.sample(k1)); new[k].append(fn.sample(k2))
-        prms.append(pde.abi_params(fn.params))
+    prms = [pde.abi_params(fn.params) for fn, _ in tasks]
+    sets = None
+    if FLAGS.gpu_samplers:                                   # all (2K + 1) x T draws in one launch, same keys (compat/gpu_samplers.py)
+        import numpy as np
+        from . import gpu_samplers
+        T = len(tasks)
+        keys = np.zeros((2 * K + 1, T, 2), np.uint32)
+        for t, (fn, rollout_key) in enumerate(tasks):
+            loss0_key, inner_keys = _rollout_keys(rollout_key, K)
+            keys[0, t] = loss0_key
+            for k in range(K):
+                keys[1 + k, t], keys[1 + K + k, t] = jr.split(inner_keys[k], 2)
+        got = gpu_samplers.sample_points_batched(pde, keys.reshape(-1, 2), tasks[0][0].n_points, [fn.params for fn, _ in tasks] * (2 * K + 1), K_)
+        if got is not None:
+            pick = lambda i: [x.reshape(2 * K + 1, T, *x.shape[1:])[i].contiguous() for x in got]
+            sets = (pick(0), [pick(1 + k) for k in range(K)], [pick(1 + K + k) for k in range(K)])
+    if sets is None:
+        loss0, step, new = [], [[] for _ in range(K)], [[] for _ in range(K)]
+        for fn, rollout_key in tasks:
+            loss0_key, inner_keys = _rollout_keys(rollout_key, K)
+            loss0.append(fn.sample(loss0_key))
+            for k in range(K):
+                k1, k2 = jr.split(inner_keys[k], 2)
+                step[k].append(fn.sample(k1)); new[k].append(fn.sample(k2))
+        sets = (_stack_points(pde, loss0), [_stack_points(pde, p) for p in step], [_stack_points(pde, p) for p in new])
     cfg = dict(inner_steps=K, inner_lr=od.learning_rate, inner_grad_clip=FLAGS.inner_grad_clip, norm=leap_def.norm,
                loss_in_distance=leap_def.loss_in_distance, stabilize=leap_def.stabilize,
                inner_opt="adam" if isinstance(od, Adam) else "sgd", beta1=getattr(od, "beta1", 0.9),
                beta2=getattr(od, "beta2", 0.99), eps=getattr(od, "eps", 1e-8))
     out = K_.leap_outer(initial_model.net_desc(K_), pde.name, tasks[0][0].bc_weight, cfg, initial_model.theta.detach().contiguous(),
-                        _stack_points(pde, loss0), [_stack_points(pde, p) for p in step], [_stack_points(pde, p) for p in new],
+                        sets[0], sets[1], sets[2],
                         torch.stack(prms).to(dev).contiguous(), len(tasks), grad_scale=scale)
     return Model(initial_model.module, out["meta_grad"]), out["losses"]

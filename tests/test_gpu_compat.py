@@ -158,6 +158,19 @@ def test_gpu_samplers_match_host_samplers(gpu_kernels, flags_small):
         (g1, l1), losses1, (meta1, _) = maml.multi_task_grad_and_losses(mdef, jr.PRNGKey(5), model, lrs)
     finally:
         FLAGS.gpu_samplers = saved
+    # LEAP's fused route (td_burgers: bit-exact points -> identical numbers)
+    bpde = pdes.get_pde("td_burgers")
+    FLAGS.inner_points = 126
+    bmodel = _model(bpde)
+    ldef = leap.LeapDef(Adam(learning_rate=1e-3, beta1=0.9, beta2=0.99).create, tasks.make_task_loss_fn_factory(bpde), 3, 2, True, True, True)
+    try:
+        FLAGS.gpu_samplers = False
+        ga, la = leap.multi_task_grad_and_losses(ldef, jr.PRNGKey(8), bmodel)
+        FLAGS.gpu_samplers = True
+        gb, lb = leap.multi_task_grad_and_losses(ldef, jr.PRNGKey(8), bmodel)
+    finally:
+        FLAGS.gpu_samplers = saved
+    assert torch.equal(ga.theta, gb.theta) and torch.equal(la, lb)
     # boundary points differ by ~1e-7 (cos / sin), the drawn candidates are the same
     assert rel_l2(g1.theta.cpu(), g0.theta.cpu()) < 1e-4 and rel_l2(l1.theta.cpu(), l0.theta.cpu()) < 1e-4
     assert rel_l2(losses1.cpu(), losses0.cpu()) < 1e-5 and rel_l2(meta1.cpu(), meta0.cpu()) < 1e-5
