@@ -51,6 +51,14 @@ WORKLOADS = {
     "dev_poisson_maml_5x256_T8_2k": dict(kind="maml", pde="poisson", L=5, W=256, T=8, n=2048, K=5),
 }
 DEFAULT_WORKLOAD = "c5_poisson_maml_5x256_T64_16k"
+
+
+def initial_theta(wl, hy, od):
+    """SIREN init (field.py:23-44), or the variance-scaling init of the --nosiren network (field.py:171-176)."""
+    from meta_pde_b200 import synthetic
+    if wl.get("act", "sin") == "swish":
+        return synthetic.swish_theta([wl["W"]] * wl["L"], od, True, seed=0)
+    return synthetic.siren_theta([wl["W"]] * wl["L"], od, hy["omega"], hy["omega"], True, seed=0)
 # pipeline/pipleline_maml_meta.sh:4 (Poisson): inner_lr 1e-4, outer_lr 1e-5, clips 100, bc_weight 1; lr_inner_lr and
 # outer_loss_decay are the flag defaults (src/maml_pde.py:52-58).  Hyperelasticity uses inner_lr 1e-5 (:6).
 HYPER = dict(inner_lr=1e-4, outer_lr=1e-5, lr_inner_lr=0.5, inner_grad_clip=100.0, grad_clip=100.0,
@@ -160,8 +168,8 @@ def _oracle_step_fn(wl, sample_tasks, n):
     pde, L, W, K, kind = wl["pde"], wl["L"], wl["W"], wl["K"], wl["kind"]
     hy = hyper_for(wl)
     od = out_dim(pde)
-    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, hy["omega"], True, od), hy["bc_weight"])
-    theta = synthetic.siren_theta([W] * L, od, hy["omega"], hy["omega"], True, seed=0)
+    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, hy["omega"], True, od, wl.get("act", "sin")), hy["bc_weight"])
+    theta = initial_theta(wl, hy, od)
     sizes = synthetic.default_set_sizes(pde, n)
     f32 = torch.float32
     mk = lambda s: synthetic.make_tasks(pde, sample_tasks, sizes, seed=s)[0]
@@ -276,7 +284,7 @@ def run_reference(args, wl, name):
 
 def bench_config(wl, name, n_gpus):
     shards = wl["T"] % n_gpus == 0 and wl["kind"] != "finetune"
-    return {"workload": name, "kind": wl["kind"], "pde": wl["pde"], "siren": f"{wl['L']}x{wl['W']} omega=30",
+    return {"workload": name, "kind": wl["kind"], "pde": wl["pde"], "siren": (f"{wl['L']}x{wl['W']} omega=30" if wl.get("act", "sin") == "sin" else f"--nosiren: {wl['L']}x{wl['W']} swish"),
             "meta_batch_tasks": wl["T"], "tasks_per_gpu": wl["T"] // n_gpus if shards else wl["T"],
             "points_per_set": wl["n"], "inner_steps": wl["K"], "second_order": wl["kind"] == "maml",
             "parallelism": f"task-sharded dp{n_gpus}" if shards else f"{n_gpus} independent replica(s)",
@@ -297,12 +305,14 @@ def build_job(wl, dev, rank, world, args):
     shards = kind != "finetune"
     T_local = T // world if shards else T
     off = rank * T_local if shards else 0
-    theta0 = synthetic.siren_theta([W] * L, out_dim(pde), hy["omega"], hy["omega"], True, seed=0)
+    theta0 = initial_theta(wl, hy, out_dim(pde))
+    act = wl.get("act", "sin")
     if kind == "maml":
         tr = train.MamlTrainer(pde, L, W, theta0, bsize=T, inner_steps=K, inner_lr=hy["inner_lr"], outer_lr=hy["outer_lr"],
                                lr_inner_lr=hy["lr_inner_lr"], siren_omega=hy["omega"], bc_weight=hy["bc_weight"],
                                inner_grad_clip=hy["inner_grad_clip"], grad_clip=hy["grad_clip"],
-                               outer_loss_decay=hy["outer_loss_decay"], device=dev, use_cuda_graph=args.graph)
+                               outer_loss_decay=hy["outer_loss_decay"], device=dev, use_cuda_graph=args.graph,
+                               nonlinearity=act)
         host = [train.synthetic_maml_batch(pde, T_local, K, n, n, seed=s, pin=True, task_offset=off, T_global=T) for s in (1, 2)]
         dev_step = lambda b, s: tr.train_step(s, b)
         host_step = lambda b, s: tr.train_step_host(s, b)
@@ -311,7 +321,7 @@ def build_job(wl, dev, rank, world, args):
     elif kind == "leap":
         tr = train.LeapTrainer(pde, L, W, theta0, bsize=T, inner_steps=K, inner_lr=hy["inner_lr"], outer_lr=hy["outer_lr"],
                                siren_omega=hy["omega"], bc_weight=hy["bc_weight"], inner_grad_clip=hy["inner_grad_clip"],
-                               grad_clip=hy["grad_clip"], device=dev)
+                               grad_clip=hy["grad_clip"], device=dev, nonlinearity=act)
         host = [train.synthetic_point_batch(pde, T_local, 1 + 2 * K, n, seed=s, pin=True, task_offset=off, T_global=T) for s in (1, 2)]
         dev_step = lambda b, s: tr.train_step(b)
         host_step = lambda b, s: tr.train_step_host(b)
@@ -319,7 +329,7 @@ def build_job(wl, dev, rank, world, args):
         packed = lambda: tr._g
     else:
         tr = train.FinetuneTrainer(pde, L, W, theta0, bsize=T, outer_lr=hy["outer_lr"], siren_omega=hy["omega"],
-                                   bc_weight=hy["bc_weight"], grad_clip=hy["grad_clip"], device=dev)
+                                   bc_weight=hy["bc_weight"], grad_clip=hy["grad_clip"], device=dev, nonlinearity=act)
         host = [train.synthetic_point_batch(pde, T_local, 1, n, seed=s, pin=True) for s in (1, 2)]
         dev_step = lambda b, s: tr.train_step(b)
         host_step = lambda b, s: tr.train_step_host(b)
@@ -448,7 +458,7 @@ def run_ours(args, wl, name):
         pass
     fp32_peak, fp32_src = 71.6, "profiles/r01_microbench_pipes.jsonl (FFMA microbench on this pool's B200, 296 CTAs)"
     tensor_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    tc = W in (128, 256) and os.environ.get("MPDE_DISABLE_TC", "0") != "1"
+    tc = W in (128, 256) and os.environ.get("MPDE_DISABLE_TC", "0") != "1" and wl.get("act", "sin") == "sin"
     dom_mode = MODE_HVP if kind == "maml" else MODE_GRAD
     roofline = None
     if prof:
@@ -542,11 +552,14 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nosiren", action="store_true",
+                    help="the reference's --nosiren network: swish hidden layers, no omega (src/maml_pde.py:115); "
+                         "FP32-FMA kernels at every width")
     ap.add_argument("--flush-l2", action="store_true", help="write 256 MB between timed steps (small, L2-resident configs)")
     ap.add_argument("--graph", action="store_true",
                     help="replay the MAML rollout as one CUDA graph (launch-bound small configs; per-kernel timing is then off)")
     args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload], act="swish" if args.nosiren else "sin")
     bench_config.graph = args.graph
     if args.impl == "reference":
         run_reference(args, wl, args.workload)

@@ -50,7 +50,7 @@ extern "C" {
 enum mpde_status {
   MPDE_OK = 0,
   MPDE_INVALID_ARG = 1,        /* null pointer, non-positive size, bad enum           */
-  MPDE_UNSUPPORTED_NET = 2,    /* width not in {32,64,128,256}, in_dim != 2, out_dim mismatch, non-SIREN */
+  MPDE_UNSUPPORTED_NET = 2,    /* width not in {32,64,128,256}, in_dim != 2, out_dim mismatch, unknown nonlinearity */
   MPDE_WORKSPACE_TOO_SMALL = 3,
   MPDE_CUDA_ERROR = 4,
   MPDE_STATIC_SCRATCH_EXCEEDED = 5   /* mpde_field_eval_static: the problem needs more than MPDE_STATIC_SCRATCH_BYTES */
@@ -58,6 +58,8 @@ enum mpde_status {
 
 enum mpde_pde_kind { MPDE_PDE_POISSON = 0, MPDE_PDE_TD_BURGERS = 1, MPDE_PDE_HYPER_ELASTICITY = 2 };
 enum mpde_mode { MPDE_MODE_LOSS = 0, MPDE_MODE_GRAD = 1, MPDE_MODE_HVP = 2 };
+
+typedef enum mpde_nonlinearity { MPDE_ACT_SIN = 0, MPDE_ACT_SWISH = 1 } mpde_nonlinearity;
 
 /* The SIREN constructor arguments of src/maml_pde.py:112-119 that reach the arithmetic. */
 typedef struct mpde_net_desc {
@@ -67,6 +69,8 @@ typedef struct mpde_net_desc {
   int32_t out_dim;     /* 1: NeuralPotential, 2: make_nf_ndim(2)           */
   float omega;         /* FLAGS.siren_omega (applied on every hidden layer, src/nets/field.py:186) */
   int32_t log_scale;   /* FLAGS.log_scale                                  */
+  int32_t nonlinearity; /* mpde_nonlinearity: 0 = np.sin (FLAGS.siren, the default), 1 = flax.nn.swish (`--nosiren`,
+                           src/maml_pde.py:115, src/nets/field.py:187-188: no omega; FP32-FMA kernels at every width) */
 } mpde_net_desc;
 
 typedef struct mpde_pde_desc {

@@ -32,7 +32,10 @@ MODE_LOSS, MODE_GRAD, MODE_HVP = 0, 1, 2
 
 class NetDesc(C.Structure):
     _fields_ = [("num_layers", C.c_int32), ("layer_size", C.c_int32), ("in_dim", C.c_int32),
-                ("out_dim", C.c_int32), ("omega", C.c_float), ("log_scale", C.c_int32)]
+                ("out_dim", C.c_int32), ("omega", C.c_float), ("log_scale", C.c_int32), ("nonlinearity", C.c_int32)]
+
+
+NONLINEARITIES = {"sin": 0, "swish": 1}   # mpde_nonlinearity (include/metapde_b200.h)
 
 
 class PdeDesc(C.Structure):
@@ -217,8 +220,12 @@ class Kernels:
     def workspace_generation(self):
         return self._ws_gen
 
-    def net_desc(self, num_layers, layer_size, out_dim, omega, log_scale=True, in_dim=2):
-        return NetDesc(int(num_layers), int(layer_size), int(in_dim), int(out_dim), float(omega), int(bool(log_scale)))
+    def net_desc(self, num_layers, layer_size, out_dim, omega, log_scale=True, in_dim=2, nonlinearity="sin"):
+        """nonlinearity: "sin" (SIREN, FLAGS.siren) or "swish" (`--nosiren`, src/maml_pde.py:115; omega is not applied)."""
+        if nonlinearity not in NONLINEARITIES:
+            raise MpdeError(f"nonlinearity {nonlinearity!r}: expected one of {sorted(NONLINEARITIES)}")
+        return NetDesc(int(num_layers), int(layer_size), int(in_dim), int(out_dim), float(omega), int(bool(log_scale)),
+                       NONLINEARITIES[nonlinearity])
 
     def pde_desc(self, pde, bc_weight, n_points):
         n = list(n_points) + [0] * (4 - len(n_points))

@@ -25,6 +25,27 @@ def sin(x):
     return torch.sin(x)
 
 
+def swish(x):
+    """The ``flax.nn.swish`` the drivers pass as ``nonlinearity`` under ``--nosiren`` (maml_pde.py:115)."""
+    return x * torch.sigmoid(x)
+
+
+def variance_scaling_fan_in_truncated_normal():
+    """field.py:171-176 (non-sin branch): variance_scaling(1.0, "fan_in", "truncated_normal") =
+    jax.random.truncated_normal(key, -2, 2) * sqrt(1 / fan_in) / 0.87962566103423978, the truncated normal drawn as
+    sqrt(2) * erfinv(U(erf(-sqrt 2), erf(sqrt 2))) from the threefry uniform of compat.random (erf/erfinv by scipy in
+    float64, rounded to float32: XLA's float32 erf_inv polynomial is not restated, so these draws are NOT pinned
+    bit-for-bit -- the distribution and the key stream are)."""
+    def init_fn(key, shape, dtype=np.float32):
+        from scipy import special
+        a, b = special.erf(-2.0 / np.sqrt(2.0)), special.erf(2.0 / np.sqrt(2.0))
+        u = np.asarray(jrandom.uniform(key, shape, minval=np.float32(a), maxval=np.float32(b)), np.float64)
+        z = np.clip(np.sqrt(2.0) * special.erfinv(u), np.nextafter(np.float32(-2.0), np.float32(0.0)),
+                    np.nextafter(np.float32(2.0), np.float32(0.0)))
+        return (z * np.sqrt(1.0 / shape[0]) / 0.87962566103423978).astype(np.float32)
+    return init_fn
+
+
 def siren_init(omega):
     """field.py:23-34: U(-sqrt(6 / fan_in) / omega, +sqrt(6 / fan_in) / omega) (threefry draws of compat.random)."""
     def init_fn(key, shape, dtype=np.float32, omega=omega):
@@ -62,9 +83,16 @@ class FieldSpec:
     def check(self):
         if self.sizes is None or len(self.sizes) < 1 or len(set(self.sizes)) != 1:
             raise NotImplementedError("metapde_b200: hidden layers must all have the same layer_size")
-        if self.nonlinearity not in (sin, np.sin, torch.sin) or self.n_fourier is not None or self.use_laaf or self.use_nlaaf:
-            raise NotImplementedError("metapde_b200: only the SIREN field (nonlinearity=np.sin, no fourier features / LAAF) "
-                                      "is implemented by the sm_100a kernels; there is no fallback path")
+        if self.nonlinearity in (sin, np.sin, torch.sin):
+            self.nonlinearity_name = "sin"
+        elif self.nonlinearity in (swish, torch.nn.functional.silu):
+            self.nonlinearity_name = "swish"
+        else:
+            raise NotImplementedError("metapde_b200: nonlinearity must be field.sin (np.sin) or field.swish (flax.nn.swish), "
+                                      "the two the reference's drivers pass; there is no fallback path")
+        if self.n_fourier is not None or self.use_laaf or self.use_nlaaf:
+            raise NotImplementedError("metapde_b200: fourier features / LAAF are not implemented by the sm_100a kernels "
+                                      "(no reference driver passes them: nn_pde.py:161-162 are commented out)")
 
     @property
     def L(self):
@@ -121,7 +149,10 @@ class _FieldBase(metaclass=_FieldMeta):
         vals = []
         for (path, shp), k in zip(shapes, keys):
             if path[-1] == "kernel":
-                init = first_layer_siren_init(spec.omega, spec.omega0) if path[0] == "Dense_0" else siren_init(spec.omega)
+                if spec.nonlinearity_name == "swish":
+                    init = variance_scaling_fan_in_truncated_normal()
+                else:
+                    init = first_layer_siren_init(spec.omega, spec.omega0) if path[0] == "Dense_0" else siren_init(spec.omega)
                 v = init(k, shp)
             elif path[-1] == "bias":
                 v = np.zeros(shp, np.float32)
@@ -207,7 +238,7 @@ class Model:
 
     def net_desc(self, K):
         s = self.spec
-        return K.net_desc(s.L, s.W, s.out_dim, s.omega, s.log_scale)
+        return K.net_desc(s.L, s.W, s.out_dim, s.omega, s.log_scale, nonlinearity=s.nonlinearity_name)
 
     def __call__(self, x):
         """field_fn(x): x [N, 2] or [2] -> [N] (1-d field) / [N, out]."""

@@ -20,7 +20,7 @@ def build(pde):
                             make_task_loss_fn=make_task_loss_fn_factory(pde), inner_steps=FLAGS.inner_steps,
                             n_batch_tasks=FLAGS.bsize, norm=True, loss_in_distance=True, stabilize=True)
     Field = pde.BaseField.partial(sizes=[FLAGS.layer_size for _ in range(FLAGS.num_layers)], dense_args=(),
-                                  nonlinearity=field.sin if FLAGS.siren else None, omega=FLAGS.siren_omega,
+                                  nonlinearity=field.sin if FLAGS.siren else field.swish, omega=FLAGS.siren_omega,
                                   omega0=FLAGS.siren_omega0, log_scale=FLAGS.log_scale)
     key, subkey = jr.split(jr.PRNGKey(0))
     _, init_params = Field.init_by_shape(subkey, [((1, 2), "float32")])

@@ -81,7 +81,7 @@ def main(argv):
     path, log, _ = trainer_util.prepare_logging(FLAGS.out_dir, FLAGS.expt_name)
     log(FLAGS.flags_into_string())
     Field = pde.BaseField.partial(sizes=[FLAGS.layer_size for _ in range(FLAGS.num_layers)], dense_args=(),
-                                  nonlinearity=field.sin if FLAGS.siren else None, omega=FLAGS.siren_omega,
+                                  nonlinearity=field.sin if FLAGS.siren else field.swish, omega=FLAGS.siren_omega,
                                   omega0=FLAGS.siren_omega0, log_scale=FLAGS.log_scale)
     key, subkey = jr.split(jr.PRNGKey(0))
     _, init_params = Field.init_by_shape(subkey, [((1, 2), "float32")])

@@ -62,7 +62,16 @@ static bool prof_begin(int mode, void* stream, cudaEvent_t* stop) {
 }
 #endif
 
-static int dispatch(int W, int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+static int dispatch(int W, int act, int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
+  if (act == MPDE_ACT_SWISH) {       // `--nosiren` network: FP32-FMA kernels at every width
+    switch (W) {
+      case 32: return dispatch_sw_w32(pde, mode, op, p, gx, gy, stream, info);
+      case 64: return dispatch_sw_w64(pde, mode, op, p, gx, gy, stream, info);
+      case 128: return dispatch_sw_w128(pde, mode, op, p, gx, gy, stream, info);
+      case 256: return dispatch_sw_w256(pde, mode, op, p, gx, gy, stream, info);
+    }
+    return MPDE_UNSUPPORTED_NET;
+  }
   switch (W) {
     case 32: return dispatch_w32(pde, mode, op, p, gx, gy, stream, info);
     case 64: return dispatch_w64(pde, mode, op, p, gx, gy, stream, info);
@@ -107,6 +116,7 @@ static int check_net(const mpde_net_desc* net, int out_dim_required) {
     return MPDE_UNSUPPORTED_NET;
   if (net->out_dim != 1 && net->out_dim != 2) return MPDE_UNSUPPORTED_NET;
   if (out_dim_required && net->out_dim != out_dim_required) return MPDE_UNSUPPORTED_NET;
+  if (net->nonlinearity != MPDE_ACT_SIN && net->nonlinearity != MPDE_ACT_SWISH) return MPDE_UNSUPPORTED_NET;
   return MPDE_OK;
 }
 
@@ -126,6 +136,7 @@ struct EvalPlan {
   // workspace sizes (floats)
   size_t n_th, n_thd, n_scratch, n_pg, n_ph, n_pt, n_gtmp;
   bool tc;                  // tensor-core path
+  int act;                  // mpde_nonlinearity
   size_t n_wimg, n_wshift;  // floats: tc weight image [T][image], shifts [T][2*TC_MAX_L]
   size_t n_rec, n_zsp, n_psmall;          // tc GRAD spills (floats) and per-CTA small-parameter partials
   size_t n_wimg_d, n_wshift_d, n_zspd, n_psmall_h;   // tc HVP: direction image / shifts, zbardot spill, H v partials
@@ -165,13 +176,14 @@ static int make_plan(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, 
     pl->term_scale[0] = 1000.f; pl->term_scale[1] = 1000.f; pl->term_scale[2] = 1.f;
     pl->weight[0] = bw; pl->weight[1] = bw; pl->weight[2] = 1.f;
   }
-  pl->tc = use_tc_path(pl->W, pl->L, mode);
+  pl->act = net->nonlinearity;
+  pl->tc = pl->act == MPDE_ACT_SIN && use_tc_path(pl->W, pl->L, mode);   // the tcgen05 epilogues are sin-jet only
 #ifndef MPDE_EMU
   if (pl->tc && mode == MODE_HVP) rc = dispatch_tc_hvp(pl->W, pl->pde, 0, nullptr, 0, 0, nullptr, &pl->ki);
   else if (pl->tc) rc = dispatch_tc(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
   else
 #endif
-  rc = dispatch(pl->W, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
+  rc = dispatch(pl->W, pl->act, pl->pde, mode, 0, nullptr, 0, 0, nullptr, &pl->ki);
   if (rc) return rc;
   const int NP = pl->ki.np;
   pl->tile_begin[0] = 0;
@@ -374,7 +386,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
     rc = dispatch_tc(pl.W, pl.pde, mode, 1, &tp, pl.G, T, stream, nullptr);
   } else
 #endif
-  rc = dispatch(pl.W, pl.pde, mode, 1, &kp, pl.G, T, stream, nullptr);
+  rc = dispatch(pl.W, pl.act, pl.pde, mode, 1, &kp, pl.G, T, stream, nullptr);
 #ifndef MPDE_EMU
   if (prof) cudaEventRecord(prof_stop, (cudaStream_t)stream);
 #endif
@@ -471,7 +483,7 @@ const char* mpde_status_string(int s) {
   switch (s) {
     case MPDE_OK: return "ok";
     case MPDE_INVALID_ARG: return "invalid argument";
-    case MPDE_UNSUPPORTED_NET: return "unsupported network (SIREN, in_dim 2, layer_size in {32,64,128,256}, out_dim matching the PDE)";
+    case MPDE_UNSUPPORTED_NET: return "unsupported network (sin or swish hidden layers, in_dim 2, layer_size in {32,64,128,256}, out_dim matching the PDE)";
     case MPDE_WORKSPACE_TOO_SMALL: return "workspace too small";
     case MPDE_CUDA_ERROR: return "CUDA error";
     case MPDE_STATIC_SCRATCH_EXCEEDED: return "problem needs more scratch than the library's static device array holds (mpde_static_scratch_bytes): use the workspace entry point";
@@ -576,7 +588,7 @@ int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t
   if (rc) return rc;
   const int kpde = (OUT == 2) ? PDE_EVAL2 : PDE_EVAL1;
   KernelInfo ki;
-  rc = dispatch(W, kpde, MODE_LOSS, 0, nullptr, 0, 0, nullptr, &ki);
+  rc = dispatch(W, net->nonlinearity, kpde, MODE_LOSS, 0, nullptr, 0, 0, nullptr, &ki);
   if (rc) return rc;
   KParams kp;
   kp.L = L; kp.P = pp.P; kp.PH = PH; kp.omega = net->omega; kp.T = T; kp.n_seg = 1;
@@ -593,7 +605,7 @@ int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t
   kp.scratch = nullptr; kp.scratch_per_cta = 0; kp.partial_g = nullptr; kp.partial_h = nullptr; kp.partial_terms = pt;
   kp.want_grad = 0;
   int G = tiles < 4096 ? tiles : 4096;
-  return dispatch(W, kpde, MODE_LOSS, 1, &kp, G, T, stream, nullptr);
+  return dispatch(W, net->nonlinearity, kpde, MODE_LOSS, 1, &kp, G, T, stream, nullptr);
 }
 
 // ------------------------------------------------------------------ samplers: jax.random on the GPU

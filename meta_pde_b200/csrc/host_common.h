@@ -38,6 +38,11 @@ int dispatch_w32(int pde, int mode, int op, const KParams* p, int gx, int gy, vo
 int dispatch_w64(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
 int dispatch_w128(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
 int dispatch_w256(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+// the same kernels with swish hidden layers (`--nosiren`, inst_sw_w*.cu)
+int dispatch_sw_w32(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+int dispatch_sw_w64(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+int dispatch_sw_w128(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
+int dispatch_sw_w256(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info);
 
 // tensor-core (tcgen05) path, widths 128 / 256 (tc_inst.cu; not part of the emulator build)
 #ifndef MPDE_EMU

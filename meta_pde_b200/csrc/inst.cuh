@@ -5,10 +5,10 @@
 
 namespace mpde {
 
-template <int W, int NTY, int PDE, int MODE>
+template <int W, int NTY, int PDE, int MODE, int ACT>
 int run_inst(int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
   typedef Geo<W, NTY> G;
-  auto kfn = pde_kernel<W, NTY, PDE, MODE>;
+  auto kfn = KernelSel<W, NTY, PDE, MODE, ACT>::fn();
   const size_t smem = G::smem_bytes(MODE);
   static int occ = 0;
 #ifndef MPDE_EMU
@@ -33,24 +33,24 @@ int run_inst(int op, const KParams* p, int gx, int gy, void* stream, KernelInfo*
   return MPDE_CHECK_LAUNCH() ? 4 : 0;
 }
 
-template <int W, int NTY, int PDE>
+template <int W, int NTY, int PDE, int ACT>
 int run_mode(int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
   switch (mode) {
-    case MODE_LOSS: return run_inst<W, NTY, PDE, MODE_LOSS>(op, p, gx, gy, stream, info);
-    case MODE_GRAD: return run_inst<W, NTY, PDE, MODE_GRAD>(op, p, gx, gy, stream, info);
-    case MODE_HVP:  return run_inst<W, NTY, PDE, MODE_HVP>(op, p, gx, gy, stream, info);
+    case MODE_LOSS: return run_inst<W, NTY, PDE, MODE_LOSS, ACT>(op, p, gx, gy, stream, info);
+    case MODE_GRAD: return run_inst<W, NTY, PDE, MODE_GRAD, ACT>(op, p, gx, gy, stream, info);
+    case MODE_HVP:  return run_inst<W, NTY, PDE, MODE_HVP, ACT>(op, p, gx, gy, stream, info);
   }
   return 1;
 }
 
-template <int W, int NTY>
+template <int W, int NTY, int ACT = ACT_SIN>
 int run_width(int pde, int mode, int op, const KParams* p, int gx, int gy, void* stream, KernelInfo* info) {
   switch (pde) {
-    case PDE_POISSON: return run_mode<W, NTY, PDE_POISSON>(mode, op, p, gx, gy, stream, info);
-    case PDE_BURGERS: return run_mode<W, NTY, PDE_BURGERS>(mode, op, p, gx, gy, stream, info);
-    case PDE_HYPER:   return run_mode<W, NTY, PDE_HYPER>(mode, op, p, gx, gy, stream, info);
-    case PDE_EVAL1:   return run_inst<W, NTY, PDE_EVAL1, MODE_LOSS>(op, p, gx, gy, stream, info);
-    case PDE_EVAL2:   return run_inst<W, NTY, PDE_EVAL2, MODE_LOSS>(op, p, gx, gy, stream, info);
+    case PDE_POISSON: return run_mode<W, NTY, PDE_POISSON, ACT>(mode, op, p, gx, gy, stream, info);
+    case PDE_BURGERS: return run_mode<W, NTY, PDE_BURGERS, ACT>(mode, op, p, gx, gy, stream, info);
+    case PDE_HYPER:   return run_mode<W, NTY, PDE_HYPER, ACT>(mode, op, p, gx, gy, stream, info);
+    case PDE_EVAL1:   return run_inst<W, NTY, PDE_EVAL1, MODE_LOSS, ACT>(op, p, gx, gy, stream, info);
+    case PDE_EVAL2:   return run_inst<W, NTY, PDE_EVAL2, MODE_LOSS, ACT>(op, p, gx, gy, stream, info);
   }
   return 1;
 }

@@ -28,9 +28,57 @@ template <> struct JetTraits<JET_XX>  { static constexpr int C = 4, NF = 5; stat
 // saved fields per element: sv = [S, Cc, p0, p1, q] (truncated to NF)
 //   S = sin(om*v), Cc = cos(om*v); the pre-activation value v itself is never needed again.
 
+// Activation kinds.  ACT_SIN is the SIREN layer sin(omega * z) (field.py:185-186); ACT_SWISH is the `--nosiren` network
+// (nonlinearity = flax.nn.swish, no omega: maml_pde.py:115, field.py:187-188).  The swish jet rules are written in the
+// derivatives g0..g4 of the activation at the value channel; the sin rules keep their closed forms.
+enum ActKind { ACT_SIN = 0, ACT_SWISH = 1 };
+
+// swish(z) = z * s(z), s = sigmoid: f_n = n * s^(n-1) + z * s^(n).  Saved fields: sv[0] = z, sv[1] = s(z).
+template <int NMAX>
+MPDE_HD void swish_derivs(float z, float s, float* g) {
+  const float s1 = s * (1.f - s);                       // s1 = ds/dz
+  g[0] = z * s;
+  g[1] = fmaf(z, s1, s);
+  if (NMAX >= 2) {
+    const float t = 1.f - 2.f * s;
+    const float s2 = s1 * t;                            // second derivative of s
+    g[2] = fmaf(z, s2, 2.f * s1);
+    if (NMAX >= 3) {
+      const float u = fmaf(6.f * s, s - 1.f, 1.f);      // 1 - 6 s + 6 s^2
+      const float s3 = s1 * u;                          // third
+      g[3] = fmaf(z, s3, 3.f * s2);
+      if (NMAX >= 4) {
+        const float s4 = s2 * u - 6.f * s1 * s1 * t;    // fourth = s2 (1 - 6s + 6s^2) + s1^2 (12 s - 6)
+        g[4] = fmaf(z, s4, 4.f * s3);
+      }
+    }
+  }
+}
+MPDE_HD float swish_sigmoid_f(float z) { return 1.f / (1.f + expf(-z)); }
+
 // a = sin-activation jet of the pre-activation jet z  (field.py:186: sin(a * omega))
-template <int JK>
+template <int JK, int ACT = ACT_SIN>
 MPDE_HD void jet_act_fwd(float om, const float* z, float* a, float* sv) {
+  if (ACT == ACT_SWISH) {
+    typedef JetTraits<JK> T;
+    float g[3];
+    const float sg = swish_sigmoid_f(z[0]);
+    swish_derivs<T::Q ? 2 : 1>(z[0], sg, g);
+    sv[0] = z[0]; sv[1] = sg;
+    a[0] = g[0];
+    if (T::C >= 3) {
+      a[1] = g[1] * z[1]; a[2] = g[1] * z[2];
+      sv[2] = z[1]; sv[3] = z[2];
+      if (T::Q) {
+        float pp = 0.f;
+        if (T::D0) pp += z[1] * z[1];
+        if (T::D1) pp += z[2] * z[2];
+        a[3] = g[1] * z[3] + g[2] * pp;
+        sv[4] = z[3];
+      }
+    }
+    return;
+  }
   typedef JetTraits<JK> T;
   float S, Cc;
   mpde_sincosf(om * z[0], &S, &Cc);
@@ -51,8 +99,24 @@ MPDE_HD void jet_act_fwd(float om, const float* z, float* a, float* sv) {
 }
 
 // same, from the saved fields (backward pass recomputes h_{l-1} from layer l-1's record)
-template <int JK>
+template <int JK, int ACT = ACT_SIN>
 MPDE_HD void jet_act_from_saved(float om, const float* sv, float* a) {
+  if (ACT == ACT_SWISH) {
+    typedef JetTraits<JK> T;
+    float g[3];
+    swish_derivs<T::Q ? 2 : 1>(sv[0], sv[1], g);
+    a[0] = g[0];
+    if (T::C >= 3) {
+      a[1] = g[1] * sv[2]; a[2] = g[1] * sv[3];
+      if (T::Q) {
+        float pp = 0.f;
+        if (T::D0) pp += sv[2] * sv[2];
+        if (T::D1) pp += sv[3] * sv[3];
+        a[3] = g[1] * sv[4] + g[2] * pp;
+      }
+    }
+    return;
+  }
   typedef JetTraits<JK> T;
   const float S = sv[0], Cc = sv[1];
   a[0] = S;
@@ -69,8 +133,30 @@ MPDE_HD void jet_act_from_saved(float om, const float* sv, float* a) {
 }
 
 // zbar = (d a / d z)^T abar
-template <int JK>
+template <int JK, int ACT = ACT_SIN>
 MPDE_HD void jet_act_bwd(float om, const float* sv, const float* ab, float* zb) {
+  if (ACT == ACT_SWISH) {
+    typedef JetTraits<JK> T;
+    float g[4];
+    swish_derivs<T::Q ? 3 : (T::C >= 3 ? 2 : 1)>(sv[0], sv[1], g);
+    float vb = g[1] * ab[0];
+    if (T::C >= 3) {
+      const float p0 = sv[2], p1 = sv[3];
+      vb += g[2] * (p0 * ab[1] + p1 * ab[2]);
+      float pb0 = g[1] * ab[1], pb1 = g[1] * ab[2];
+      if (T::Q) {
+        const float q = sv[4], aq = ab[3];
+        float pp = 0.f;
+        if (T::D0) { pp += p0 * p0; pb0 += 2.f * g[2] * p0 * aq; }
+        if (T::D1) { pp += p1 * p1; pb1 += 2.f * g[2] * p1 * aq; }
+        vb += (g[2] * q + g[3] * pp) * aq;
+        zb[3] = g[1] * aq;
+      }
+      zb[1] = pb0; zb[2] = pb1;
+    }
+    zb[0] = vb;
+    return;
+  }
   typedef JetTraits<JK> T;
   const float S = sv[0], Cc = sv[1];
   const float oc = om * Cc, o2s = om * om * S;
@@ -93,8 +179,28 @@ MPDE_HD void jet_act_bwd(float om, const float* sv, const float* ab, float* zb) 
 }
 
 // adot = (d a / d z) zdot
-template <int JK>
+template <int JK, int ACT = ACT_SIN>
 MPDE_HD void jet_act_tan(float om, const float* sv, const float* zd, float* ad) {
+  if (ACT == ACT_SWISH) {
+    typedef JetTraits<JK> T;
+    float g[4];
+    swish_derivs<T::Q ? 3 : (T::C >= 3 ? 2 : 1)>(sv[0], sv[1], g);
+    const float vd = zd[0];
+    ad[0] = g[1] * vd;
+    if (T::C >= 3) {
+      const float p0 = sv[2], p1 = sv[3];
+      ad[1] = g[1] * zd[1] + g[2] * p0 * vd;
+      ad[2] = g[1] * zd[2] + g[2] * p1 * vd;
+      if (T::Q) {
+        const float q = sv[4];
+        float pp = 0.f, ppd = 0.f;
+        if (T::D0) { pp += p0 * p0; ppd += p0 * zd[1]; }
+        if (T::D1) { pp += p1 * p1; ppd += p1 * zd[2]; }
+        ad[3] = g[1] * zd[3] + g[2] * q * vd + 2.f * g[2] * ppd + g[3] * pp * vd;
+      }
+    }
+    return;
+  }
   typedef JetTraits<JK> T;
   const float S = sv[0], Cc = sv[1];
   const float oc = om * Cc, o2s = om * om * S;
@@ -115,9 +221,42 @@ MPDE_HD void jet_act_tan(float om, const float* sv, const float* zd, float* ad) 
 }
 
 // zbardot = d/d eps [ (d a / d z)^T abar ] along (zdot, abardot)
-template <int JK>
+template <int JK, int ACT = ACT_SIN>
 MPDE_HD void jet_act_bwd_tan(float om, const float* sv, const float* zd, const float* ab, const float* abd,
                              float* zbd) {
+  if (ACT == ACT_SWISH) {
+    typedef JetTraits<JK> T;
+    float g[5];
+    swish_derivs<T::Q ? 4 : (T::C >= 3 ? 3 : 2)>(sv[0], sv[1], g);
+    const float vd = zd[0];
+    float vbd = g[1] * abd[0] + g[2] * vd * ab[0];
+    if (T::C >= 3) {
+      const float p0 = sv[2], p1 = sv[3];
+      const float pd0 = zd[1], pd1 = zd[2];
+      float pbd0 = g[1] * abd[1] + g[2] * vd * ab[1];
+      float pbd1 = g[1] * abd[2] + g[2] * vd * ab[2];
+      vbd += g[2] * (p0 * abd[1] + p1 * abd[2]) + g[2] * (pd0 * ab[1] + pd1 * ab[2]) +
+             g[3] * vd * (p0 * ab[1] + p1 * ab[2]);
+      if (T::Q) {
+        const float q = sv[4], qd = zd[3], aq = ab[3], aqd = abd[3];
+        float pp = 0.f, ppd = 0.f;
+        if (T::D0) {
+          pp += p0 * p0; ppd += p0 * pd0;
+          pbd0 += 2.f * (g[2] * (p0 * aqd + pd0 * aq) + g[3] * vd * p0 * aq);
+        }
+        if (T::D1) {
+          pp += p1 * p1; ppd += p1 * pd1;
+          pbd1 += 2.f * (g[2] * (p1 * aqd + pd1 * aq) + g[3] * vd * p1 * aq);
+        }
+        vbd += (g[2] * q + g[3] * pp) * aqd;
+        vbd += (g[2] * qd + g[3] * vd * q + 2.f * g[3] * ppd + g[4] * vd * pp) * aq;
+        zbd[3] = g[1] * aqd + g[2] * vd * aq;
+      }
+      zbd[1] = pbd0; zbd[2] = pbd1;
+    }
+    zbd[0] = vbd;
+    return;
+  }
   typedef JetTraits<JK> T;
   const float S = sv[0], Cc = sv[1];
   const float oc = om * Cc, o2s = om * om * S, o3c = om * om * oc, o4s = om * om * o2s;

@@ -212,7 +212,7 @@ template <int JK, int MODE> struct Rec {
 };
 
 // Per-tile processing ---------------------------------------------------------
-template <int W, int NTY, int HEAD, int MODE>
+template <int W, int NTY, int HEAD, int MODE, int ACT = ACT_SIN>
 struct Tile {
   typedef Geo<W, NTY> G;
   typedef HeadTraits<HEAD> HT;
@@ -244,7 +244,7 @@ struct Tile {
           float z[C], a[C], sv[NF];
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) z[c] = acc[VAL ? e : c][i][j];
-          jet_act_fwd<JK>(om, z, a, sv);
+          jet_act_fwd<JK, ACT>(om, z, a, sv);
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) acc[VAL ? e : c][i][j] = a[c];
           MPDE_UNROLL
@@ -277,7 +277,7 @@ struct Tile {
           for (int f = 0; f < NF; ++f) sv[f] = (i == 0 ? svv[f].x : i == 1 ? svv[f].y : i == 2 ? svv[f].z : svv[f].w);
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) { zd[c] = accd[VAL ? e : c][i][j]; zdv[c][i] = zd[c]; }
-          jet_act_tan<JK>(om, sv, zd, ad);
+          jet_act_tan<JK, ACT>(om, sv, zd, ad);
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) accd[VAL ? e : c][i][j] = ad[c];
         }
@@ -313,9 +313,9 @@ struct Tile {
             float zd[C];
             MPDE_UNROLL
             for (int c = 0; c < C; ++c) zd[c] = (i == 0 ? zdv[c].x : i == 1 ? zdv[c].y : i == 2 ? zdv[c].z : zdv[c].w);
-            jet_act_tan<JK>(om, sv, zd, a);
+            jet_act_tan<JK, ACT>(om, sv, zd, a);
           } else {
-            jet_act_from_saved<JK>(om, sv, a);
+            jet_act_from_saved<JK, ACT>(om, sv, a);
           }
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) out[VAL ? e : c][i][j] = a[c];
@@ -345,7 +345,7 @@ struct Tile {
           for (int f = 0; f < NF; ++f) sv[f] = (i == 0 ? svv[f].x : i == 1 ? svv[f].y : i == 2 ? svv[f].z : svv[f].w);
           MPDE_UNROLL
           for (int c = 0; c < C; ++c) a_[c] = ab[VAL ? e : c][i][j];
-          jet_act_bwd<JK>(om, sv, a_, zb);
+          jet_act_bwd<JK, ACT>(om, sv, a_, zb);
           if (MODE == MODE_HVP) {
             float zd[C], ad_[C], zbd[C];
             MPDE_UNROLL
@@ -353,7 +353,7 @@ struct Tile {
               zd[c] = (i == 0 ? zdv[c].x : i == 1 ? zdv[c].y : i == 2 ? zdv[c].z : zdv[c].w);
               ad_[c] = abd[VAL ? e : c][i][j];
             }
-            jet_act_bwd_tan<JK>(om, sv, zd, a_, ad_, zbd);
+            jet_act_bwd_tan<JK, ACT>(om, sv, zd, a_, ad_, zbd);
             MPDE_UNROLL
             for (int c = 0; c < C; ++c) abd[VAL ? e : c][i][j] = zbd[c];
           }
@@ -740,8 +740,8 @@ struct Tile {
 // ---------------------------------------------------------------------------
 // kernel: grid = (ctas_per_task, T); each CTA walks the task's tiles with stride gridDim.x
 // ---------------------------------------------------------------------------
-template <int W, int NTY, int PDE, int MODE>
-MPDE_GLOBAL void MPDE_LAUNCH_BOUNDS((Geo<W, NTY>::NT), 1) pde_kernel(KParams p) {
+template <int W, int NTY, int PDE, int MODE, int ACT>
+MPDE_DEV void pde_kernel_body(const KParams& p) {
   typedef Geo<W, NTY> G;
   float* smem = reinterpret_cast<float*>(mpde_smem());
   const int tid = threadIdx.x;
@@ -780,23 +780,41 @@ MPDE_GLOBAL void MPDE_LAUNCH_BOUNDS((Geo<W, NTY>::NT), 1) pde_kernel(KParams p) 
     const int tile = t - p.seg_tile_begin[s];
     const SegDesc& sg = p.seg[s];
     if (PDE == PDE_POISSON) {
-      if (sg.head == HEAD_POISSON_DOMAIN) Tile<W, NTY, HEAD_POISSON_DOMAIN, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
-      else Tile<W, NTY, HEAD_POISSON_BOUNDARY, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      if (sg.head == HEAD_POISSON_DOMAIN) Tile<W, NTY, HEAD_POISSON_DOMAIN, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      else Tile<W, NTY, HEAD_POISSON_BOUNDARY, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
     } else if (PDE == PDE_BURGERS) {
-      if (sg.head == HEAD_BURGERS_DOMAIN) Tile<W, NTY, HEAD_BURGERS_DOMAIN, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
-      else Tile<W, NTY, HEAD_BURGERS_IC, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      if (sg.head == HEAD_BURGERS_DOMAIN) Tile<W, NTY, HEAD_BURGERS_DOMAIN, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      else Tile<W, NTY, HEAD_BURGERS_IC, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
     } else if (PDE == PDE_HYPER) {
-      if (sg.head == HEAD_HYPER_DOMAIN) Tile<W, NTY, HEAD_HYPER_DOMAIN, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
-      else if (sg.head == HEAD_HYPER_TOP) Tile<W, NTY, HEAD_HYPER_TOP, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
-      else Tile<W, NTY, HEAD_HYPER_BOTTOM, MODE>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      if (sg.head == HEAD_HYPER_DOMAIN) Tile<W, NTY, HEAD_HYPER_DOMAIN, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      else if (sg.head == HEAD_HYPER_TOP) Tile<W, NTY, HEAD_HYPER_TOP, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      else Tile<W, NTY, HEAD_HYPER_BOTTOM, MODE, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
     } else if (PDE == PDE_EVAL1) {
-      Tile<W, NTY, HEAD_EVAL, MODE_LOSS>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      Tile<W, NTY, HEAD_EVAL, MODE_LOSS, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
     } else {
-      Tile<W, NTY, HEAD_EVAL2, MODE_LOSS>::run(p, sg, s, task, tile, smem, scr, pg, ph);
+      Tile<W, NTY, HEAD_EVAL2, MODE_LOSS, ACT>::run(p, sg, s, task, tile, smem, scr, pg, ph);
     }
   }
   __syncthreads();
   if (tid < MAX_SEG) p.partial_terms[(size_t)cta * MAX_SEG + tid] = terms[tid];
 }
+
+// SIREN network (the published configurations)
+template <int W, int NTY, int PDE, int MODE>
+MPDE_GLOBAL void MPDE_LAUNCH_BOUNDS((Geo<W, NTY>::NT), 1) pde_kernel(KParams p) {
+  pde_kernel_body<W, NTY, PDE, MODE, ACT_SIN>(p);
+}
+// `--nosiren` network: swish hidden layers, no omega (maml_pde.py:115, field.py:187-188)
+template <int W, int NTY, int PDE, int MODE>
+MPDE_GLOBAL void MPDE_LAUNCH_BOUNDS((Geo<W, NTY>::NT), 1) pde_kernel_swish(KParams p) {
+  pde_kernel_body<W, NTY, PDE, MODE, ACT_SWISH>(p);
+}
+template <int W, int NTY, int PDE, int MODE, int ACT> struct KernelSel;
+template <int W, int NTY, int PDE, int MODE> struct KernelSel<W, NTY, PDE, MODE, ACT_SIN> {
+  static constexpr auto fn() { return pde_kernel<W, NTY, PDE, MODE>; }
+};
+template <int W, int NTY, int PDE, int MODE> struct KernelSel<W, NTY, PDE, MODE, ACT_SWISH> {
+  static constexpr auto fn() { return pde_kernel_swish<W, NTY, PDE, MODE>; }
+};
 
 }  // namespace mpde

@@ -36,6 +36,24 @@ def siren_theta(sizes, out_dim=1, omega=30.0, omega0=30.0, log_scale=True, io_sc
     return torch.cat(parts).to(dtype)
 
 
+def swish_theta(sizes, out_dim=1, log_scale=True, io_scale_lr_factor=10.0, seed=0, bias_scale=0.0, in_dim=2,
+                dtype=torch.float32):
+    """Flat theta of the `--nosiren` network (src/nets/field.py:171-176: variance_scaling(1.0, "fan_in",
+    "truncated_normal") on every kernel): N(0, 1 / fan_in) truncated at 2 sigma, rescaled by 1 / 0.8796..."""
+    g = torch.Generator().manual_seed(int(seed))
+    parts = []
+    n_in = in_dim
+    for n_out in list(sizes) + [out_dim]:
+        z = torch.randn(n_in, n_out, generator=g, dtype=torch.float64).clamp(-2.0, 2.0)
+        parts.append((z * math.sqrt(1.0 / n_in) / 0.87962566103423978).reshape(-1))
+        parts.append(bias_scale * torch.randn(n_out, generator=g, dtype=torch.float64))
+        n_in = n_out
+    if log_scale:
+        parts.append(torch.full((in_dim,), math.log(1.0 / io_scale_lr_factor), dtype=torch.float64))
+        parts.append(torch.full((out_dim,), math.log(1.0 / io_scale_lr_factor), dtype=torch.float64))
+    return torch.cat(parts).to(dtype)
+
+
 def default_set_sizes(pde, n):
     """Point-set sizes the reference samplers produce for ``n`` requested points."""
     if pde == "poisson":

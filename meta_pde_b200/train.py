@@ -93,13 +93,14 @@ class MamlTrainer:
 
     def __init__(self, pde, num_layers, layer_size, theta0, *, bsize, inner_steps, inner_lr, outer_lr, lr_inner_lr,
                  siren_omega=30.0, log_scale=True, bc_weight=1.0, inner_grad_clip=1e14, grad_clip=1e14,
-                 outer_loss_decay=0.1, optimizer="adam", device=None, group=None, use_cuda_graph=False, kernels=None):
+                 outer_loss_decay=0.1, optimizer="adam", device=None, group=None, use_cuda_graph=False, kernels=None,
+                 nonlinearity="sin"):
         # `kernels` is for the CPU tests, which bind the emulator build of the kernel sources; the product path is
         # ops.kernels(), which raises without CUDA / without the built library (no CPU fallback)
         self.K = kernels if kernels is not None else ops.kernels(device)
         self.device = self.K.device
         self.pde = pde
-        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale)
+        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale, nonlinearity=nonlinearity)
         self.P = self.K.param_count(self.net)
         if theta0.numel() != self.P:
             raise ValueError(f"theta0 has {theta0.numel()} parameters, the network needs {self.P}")
@@ -320,10 +321,10 @@ class LeapTrainer(_OuterOpt):
 
     def __init__(self, pde, num_layers, layer_size, theta0, *, bsize, inner_steps, inner_lr, outer_lr, siren_omega=30.0,
                  log_scale=True, bc_weight=1.0, inner_grad_clip=1e14, grad_clip=1e14, optimizer="adam", inner_opt="adam",
-                 device=None, group=None, kernels=None):
+                 device=None, group=None, kernels=None, nonlinearity="sin"):
         self.K = kernels if kernels is not None else ops.kernels(device)
         self.device, self.pde = self.K.device, pde
-        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale)
+        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale, nonlinearity=nonlinearity)
         self.P = self.K.param_count(self.net)
         self.bsize, self.inner_steps, self.bc_weight = int(bsize), int(inner_steps), float(bc_weight)
         self.cfg = dict(inner_steps=self.inner_steps, inner_lr=float(inner_lr), inner_grad_clip=float(inner_grad_clip),
@@ -357,10 +358,10 @@ class FinetuneTrainer(_OuterOpt):
     (bsize = 1 in the published command): replicas only."""
 
     def __init__(self, pde, num_layers, layer_size, theta0, *, bsize, outer_lr, siren_omega=30.0, log_scale=True,
-                 bc_weight=1.0, grad_clip=1e14, optimizer="adam", device=None, kernels=None):
+                 bc_weight=1.0, grad_clip=1e14, optimizer="adam", device=None, kernels=None, nonlinearity="sin"):
         self.K = kernels if kernels is not None else ops.kernels(device)
         self.device, self.pde = self.K.device, pde
-        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale)
+        self.net = self.K.net_desc(num_layers, layer_size, PDE_OUT_DIM[pde], siren_omega, log_scale, nonlinearity=nonlinearity)
         self.P = self.K.param_count(self.net)
         self.bsize, self.bc_weight = int(bsize), float(bc_weight)
         self._init_opt(theta0, optimizer, outer_lr, grad_clip)

@@ -117,9 +117,11 @@ def param_count(sizes, in_dim=2, out_dim=1, log_scale=True):
 
 
 # ----------------------------------------------------------------------------
-# nf_apply (field.py:146-199), nonlinearity = sin only (the published runs)
+# nf_apply (field.py:146-199): nonlinearity = np.sin (FLAGS.siren, the published runs; field.py:185-186 applies omega) or
+# flax.nn.swish (`--nosiren`, maml_pde.py:115; field.py:187-188: no omega).  n_fourier / LAAF are never passed by a driver.
 # ----------------------------------------------------------------------------
-def nf_apply(params, out_dim, x, omega=30.0):
+def nf_apply(params, out_dim, x, omega=30.0, nonlinearity="sin"):
+    assert nonlinearity in ("sin", "swish"), nonlinearity
     log_scale = "log_input_scale" in params
     if log_scale:
         in_scale = torch.exp(params["log_input_scale"])
@@ -128,7 +130,7 @@ def nf_apply(params, out_dim, x, omega=30.0):
     for i in range(n - 1):
         d = params[f"Dense_{i}"]
         a = x @ d["kernel"] + d["bias"]
-        x = torch.sin(a * omega)
+        x = torch.sin(a * omega) if nonlinearity == "sin" else a * torch.sigmoid(a)
     d = params[f"Dense_{n - 1}"]
     out = x @ d["kernel"] + d["bias"]
     if log_scale:
@@ -137,21 +139,21 @@ def nf_apply(params, out_dim, x, omega=30.0):
     return out
 
 
-def neural_field_1d(params, x, omega=30.0):
+def neural_field_1d(params, x, omega=30.0, nonlinearity="sin"):
     """NeuralField1d / NeuralPotential (field.py:212-216,259)."""
-    return nf_apply(params, 1, x, omega).sum(dim=-1)
+    return nf_apply(params, 1, x, omega, nonlinearity).sum(dim=-1)
 
 
-def neural_field_nd(params, x, n_dims, omega=30.0):
+def neural_field_nd(params, x, n_dims, omega=30.0, nonlinearity="sin"):
     """make_nf_ndim(n_dims) (field.py:219-226)."""
-    return nf_apply(params, n_dims, x, omega)
+    return nf_apply(params, n_dims, x, omega, nonlinearity)
 
 
-def make_field_fn(params, out_dim, omega):
+def make_field_fn(params, out_dim, omega, nonlinearity="sin"):
     """The callable the reference hands to pde.loss_fn (a flax.nn.Model)."""
     if out_dim == 1:
-        return lambda x: neural_field_1d(params, x, omega)
-    return lambda x: neural_field_nd(params, x, out_dim, omega)
+        return lambda x: neural_field_1d(params, x, omega, nonlinearity)
+    return lambda x: neural_field_nd(params, x, out_dim, omega, nonlinearity)
 
 
 # ----------------------------------------------------------------------------

@@ -29,7 +29,7 @@ import torch.nn.functional as F
 from .field import unflatten_params, make_field_fn
 from .pdes import driver_loss, PDE_OUT_DIM, PDE_TERMS
 
-NetCfg = namedtuple("NetCfg", ["sizes", "omega", "log_scale", "out_dim"])
+NetCfg = namedtuple("NetCfg", ["sizes", "omega", "log_scale", "out_dim", "nonlinearity"], defaults=("sin",))
 
 
 def make_loss_fn(pde_name, net, bc_weight):
@@ -37,7 +37,7 @@ def make_loss_fn(pde_name, net, bc_weight):
 
     def loss_fn(theta, points, pde_params):
         params = unflatten_params(theta, net.sizes, 2, net.out_dim, net.log_scale)
-        field_fn = make_field_fn(params, net.out_dim, net.omega)
+        field_fn = make_field_fn(params, net.out_dim, net.omega, net.nonlinearity)
         return driver_loss(pde_name, field_fn, points, pde_params, bc_weight)
 
     return loss_fn

@@ -166,8 +166,16 @@ def make_driver(pde):
     return loss_fn
 
 
+ACT = "sin"   # "swish": the `--nosiren` network (nonlinearity=nn.swish, src/maml_pde.py:115); set by main()
+
+
+def _sfx():
+    return "" if ACT == "sin" else "_" + ACT
+
+
 def build_model(pde, W, L, seed, bias_scale=0.05):
-    Field = BASE_FIELD[pde].partial(sizes=[W] * L, dense_args=(), nonlinearity=np.sin, omega=FLAGS.siren_omega,
+    Field = BASE_FIELD[pde].partial(sizes=[W] * L, dense_args=(), nonlinearity=np.sin if ACT == "sin" else flax.nn.swish,
+                                    omega=FLAGS.siren_omega,
                                     omega0=FLAGS.siren_omega0, log_scale=FLAGS.log_scale)      # src/maml_pde.py:112-119
     key, subkey = jax.random.split(jax.random.PRNGKey(seed))
     _, init_params = Field.init_by_shape(subkey, [((1, 2), np.float32)])                        # src/maml_pde.py:121-124
@@ -184,7 +192,7 @@ class Recorder:
 
 
 def save(name, **arrays):
-    out = {}
+    out = {"act": onp.array(0 if ACT == "sin" else 1)}
     for k, v in arrays.items():
         if torch.is_tensor(v):
             v = v.detach().cpu().numpy()
@@ -232,7 +240,7 @@ def fixture_loss_grad(pde, W, L, n, T, seed):
                   meta=onp.array([W, L, T, PDE_OUT_DIM[pde]]), omega=FLAGS.siren_omega, bc_weight=FLAGS.bc_weight)
     for s, x in enumerate(stack_sets(sets)):
         arrays[f"set{s}"] = x
-    save(f"ref_loss_{pde}_{L}x{W}", **arrays)
+    save(f"ref_loss_{pde}_{L}x{W}{_sfx()}", **arrays)
 
 
 def fixture_maml(pde, W, L, n, T, K, seed, inner_lr, clip, decay):
@@ -301,7 +309,7 @@ def fixture_maml(pde, W, L, n, T, K, seed, inner_lr, clip, decay):
     for s, x in enumerate(stack_sets(auxp)):
         arrays[f"aux_set{s}"] = x
     tag = "clip" if clip < 1e10 else "noclip"
-    save(f"ref_maml_{pde}_{L}x{W}_{tag}", **arrays)
+    save(f"ref_maml_{pde}_{L}x{W}_{tag}{_sfx()}", **arrays)
     FLAGS.inner_grad_clip = 1e14
 
 
@@ -348,11 +356,27 @@ def fixture_leap(pde, W, L, n, T, K, seed, inner_lr, clip):
             arrays[f"step{k}_set{s}"] = x
         for s, x in enumerate(stack_sets(new[k])):
             arrays[f"new{k}_set{s}"] = x
-    save(f"ref_leap_{pde}_{L}x{W}", **arrays)
+    save(f"ref_leap_{pde}_{L}x{W}{_sfx()}", **arrays)
     FLAGS.inner_grad_clip = 1e14
 
 
+def main_swish():
+    """Row f4: the same reference functions with nonlinearity = flax.nn.swish (no omega, field.py:187-188)."""
+    global ACT
+    ACT = "swish"
+    torch.manual_seed(0)
+    for pde in ("poisson", "td_burgers", "hyper_elasticity"):
+        fixture_loss_grad(pde, 32, 2, 24, 2, seed=41)
+    fixture_loss_grad("poisson", 64, 3, 40, 1, seed=42)
+    fixture_maml("poisson", 32, 2, 16, 2, 2, seed=51, inner_lr=1e-2, clip=1e14, decay=0.1)
+    fixture_maml("td_burgers", 32, 2, 16, 2, 2, seed=52, inner_lr=1e-2, clip=1e-2, decay=0.5)
+    fixture_leap("hyper_elasticity", 32, 2, 16, 2, 2, seed=61, inner_lr=1e-4, clip=1e14)
+    ACT = "sin"
+
+
 def main():
+    if "--only-swish" in sys.argv[1:]:
+        return main_swish()
     torch.manual_seed(0)
     for pde in ("poisson", "td_burgers", "hyper_elasticity"):
         fixture_loss_grad(pde, 32, 2, 24, 2, seed=11)
@@ -370,6 +394,7 @@ def main():
     fixture_maml("poisson", 128, 2, 16, 2, 2, seed=23, inner_lr=1e-2, clip=1e14, decay=0.1)
     fixture_maml("td_burgers", 128, 2, 70, 2, 2, seed=24, inner_lr=1e-2, clip=1e-2, decay=0.1)
     fixture_leap("poisson", 128, 2, 16, 2, 2, seed=33, inner_lr=1e-3, clip=1e14)
+    main_swish()
 
 
 if __name__ == "__main__":

@@ -29,6 +29,7 @@ def load(name):
     kind = parts[1]
     pde = "_".join(parts[2:]).split("_2x")[0].split("_3x")[0]
     d["_pde"], d["_kind"] = pde, kind
+    d["_act"] = "swish" if int(d.get("act", torch.tensor(0))) else "sin"   # fixtures of the `--nosiren` network carry act = 1
     return d
 
 
@@ -46,7 +47,7 @@ def oracle_vs_loss_fixture(name):
     d = load(name)
     pde = d["_pde"]
     W, L, T, out = (int(x) for x in d["meta"])
-    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, float(d["omega"]), True, out), float(d["bc_weight"]))
+    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, float(d["omega"]), True, out, d["_act"]), float(d["bc_weight"]))
     sets = _sets(d, "", pde)
     errs = {}
     for t in range(T):
@@ -54,7 +55,7 @@ def oracle_vs_loss_fixture(name):
         pts, prm = oracle_points(pde, sets, t), oracle_params(pde, d["pde_params"], t)
         l, aux = lf(th, pts, prm)
         (g,) = torch.autograd.grad(l, th)
-        ffn = make_field_fn(unflatten_params(d["theta"].double(), [W] * L, 2, out, True), out, float(d["omega"]))
+        ffn = make_field_fn(unflatten_params(d["theta"].double(), [W] * L, 2, out, True), out, float(d["omega"]), d["_act"])
         if pde == "poisson":
             q = opdes.poisson_residual(ffn, pts[1], prm[0])
         elif pde == "td_burgers":
@@ -82,7 +83,7 @@ def oracle_vs_maml_fixture(name):
     pde = d["_pde"]
     W, L, T, out, K = (int(x) for x in d["meta"])
     inner_lr, clip, decay = (float(x) for x in d["hyper"])
-    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, float(d["omega"]), True, out), float(d["bc_weight"]))
+    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, float(d["omega"]), True, out, d["_act"]), float(d["bc_weight"]))
     cfg = ometa.MamlCfg(K, inner_lr, clip, True, decay)
     (g_theta, g_lrs), losses, (meta, aux) = ometa.maml_multi_task_grad_and_losses(
         cfg, lf, d["theta"].double(), _maml_tasks(d, pde, T, K), d["inner_lrs"].double())
@@ -103,7 +104,7 @@ def oracle_vs_leap_fixture(name):
     pde = d["_pde"]
     W, L, T, out, K = (int(x) for x in d["meta"])
     inner_lr, clip = (float(x) for x in d["hyper"])
-    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, float(d["omega"]), True, out), float(d["bc_weight"]))
+    lf = ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, float(d["omega"]), True, out, d["_act"]), float(d["bc_weight"]))
     cfg = ometa.LeapCfg(K, inner_lr, clip, True, True, True, "adam")
     mg, losses = ometa.leap_multi_task_grad_and_losses(cfg, lf, d["theta"].double(), _leap_tasks(d, pde, T, K))
     errs = {"meta_grad": rel_l2(mg, d["meta_grad"]), "losses": rel_l2(losses, d["losses"])}
@@ -120,7 +121,7 @@ def kernels_vs_loss_fixture(K, name):
     d = load(name)
     pde = d["_pde"]
     W, L, T, out = (int(x) for x in d["meta"])
-    net = K.net_desc(L, W, out, float(d["omega"]), True)
+    net = K.net_desc(L, W, out, float(d["omega"]), True, nonlinearity=d["_act"])
     sets = [_dev(K, s) for s in _sets(d, "", pde)]
     bw = float(d["bc_weight"])
     loss, terms, res = K.loss(net, pde, bw, _dev(K, d["theta"]), sets, _dev(K, d["pde_params"]), T, want_residual=True)
@@ -138,7 +139,7 @@ def kernels_vs_maml_fixture(K, name):
     pde = d["_pde"]
     W, L, T, out, Ks = (int(x) for x in d["meta"])
     inner_lr, clip, decay = (float(x) for x in d["hyper"])
-    net = K.net_desc(L, W, out, float(d["omega"]), True)
+    net = K.net_desc(L, W, out, float(d["omega"]), True, nonlinearity=d["_act"])
     cfg = dict(inner_steps=Ks, inner_lr=inner_lr, inner_grad_clip=clip, softplus_lrs=True, outer_loss_decay=decay)
     S = lambda pre: [_dev(K, s) for s in _sets(d, pre, pde)]
     got = K.maml_outer(net, pde, float(d["bc_weight"]), cfg, _dev(K, d["theta"]), _dev(K, d["inner_lrs"]),
@@ -153,7 +154,7 @@ def kernels_vs_leap_fixture(K, name):
     pde = d["_pde"]
     W, L, T, out, Ks = (int(x) for x in d["meta"])
     inner_lr, clip = (float(x) for x in d["hyper"])
-    net = K.net_desc(L, W, out, float(d["omega"]), True)
+    net = K.net_desc(L, W, out, float(d["omega"]), True, nonlinearity=d["_act"])
     cfg = dict(inner_steps=Ks, inner_lr=inner_lr, inner_grad_clip=clip, norm=True, loss_in_distance=True, stabilize=True,
                inner_opt="adam", beta1=0.9, beta2=0.99, eps=1e-8)
     S = lambda pre: [_dev(K, s) for s in _sets(d, pre, pde)]

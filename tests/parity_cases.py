@@ -15,6 +15,28 @@ from oracle import pdes as opdes
 
 TOL = 1e-4  # BASELINE.json north_star: "relative 1e-4 on residuals, losses, inner-updated params and outer gradients"
 OMEGA = 30.0
+ACT = "sin"   # hidden nonlinearity of the cases below; `with nonlinearity("swish"):` runs them on the `--nosiren` network
+
+
+class nonlinearity:
+    """Run the checkers of this module with another hidden nonlinearity (maml_pde.py:115)."""
+
+    def __init__(self, act):
+        self.act = act
+
+    def __enter__(self):
+        global ACT
+        self.prev, ACT = ACT, self.act
+
+    def __exit__(self, *exc):
+        global ACT
+        ACT = self.prev
+
+
+def _theta(sizes, out_dim, omega, omega0, log_scale, seed=0, bias_scale=0.0):
+    if ACT == "sin":
+        return synthetic.siren_theta(sizes, out_dim, omega, omega0, log_scale, seed=seed, bias_scale=bias_scale)
+    return synthetic.swish_theta(sizes, out_dim, log_scale, seed=seed, bias_scale=bias_scale)
 
 
 def _tol(name, theta_K, theta0):
@@ -31,7 +53,7 @@ def _dev(K, x):
 
 def make_problem(pde, W, L, n, T, seed=0, per_task_theta=True, set_sizes=None):
     out = PDE_OUT_DIM[pde]
-    theta = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     if per_task_theta:
         g = torch.Generator().manual_seed(seed + 100)
         theta = torch.stack([theta * (1.0 + 0.02 * t) + 1e-3 * torch.randn(theta.numel(), generator=g) for t in range(T)])
@@ -41,14 +63,14 @@ def make_problem(pde, W, L, n, T, seed=0, per_task_theta=True, set_sizes=None):
 
 
 def oracle_loss_fn(pde, W, L, bc_weight=1.0):
-    return ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, OMEGA, True, PDE_OUT_DIM[pde]), bc_weight)
+    return ometa.make_loss_fn(pde, ometa.NetCfg([W] * L, OMEGA, True, PDE_OUT_DIM[pde], ACT), bc_weight)
 
 
 def check_loss_grad_hvp(K, pde, W, L, n, T, bc_weight=1.0, seed=0, set_sizes=None, per_task_theta=True):
     theta, sets, prm = make_problem(pde, W, L, n, T, seed, per_task_theta, set_sizes)
     P = theta.shape[-1]
     v = torch.randn(T, P, generator=torch.Generator().manual_seed(seed + 7))
-    net = K.net_desc(L, W, PDE_OUT_DIM[pde], OMEGA, True)
+    net = K.net_desc(L, W, PDE_OUT_DIM[pde], OMEGA, True, nonlinearity=ACT)
     dsets = [_dev(K, s) for s in sets]
     loss0, terms0, res = K.loss(net, pde, bc_weight, _dev(K, theta), dsets, _dev(K, prm), T, want_residual=True)
     loss1, terms1, grad1 = K.loss_grad(net, pde, bc_weight, _dev(K, theta), dsets, _dev(K, prm), T)
@@ -65,7 +87,7 @@ def check_loss_grad_hvp(K, pde, W, L, n, T, bc_weight=1.0, seed=0, set_sizes=Non
         ot = torch.stack([aux[k].detach() for k in PDE_TERMS[pde]])
         # per-point residual / energy density
         params = unflatten_params(th0.double(), [W] * L, 2, PDE_OUT_DIM[pde], True)
-        ffn = make_field_fn(params, PDE_OUT_DIM[pde], OMEGA)
+        ffn = make_field_fn(params, PDE_OUT_DIM[pde], OMEGA, ACT)
         if pde == "poisson":
             r = opdes.poisson_residual(ffn, pts[1], prm_t[0])
         elif pde == "td_burgers":
@@ -102,13 +124,13 @@ def make_maml_data(pde, n_in, n_out, T, K_steps, seed):
 
 def check_maml(K, pde, W, L, n, T, K_steps=2, inner_lr=1e-3, clip=1e14, decay=0.1, lr_tree=True, seed=0, bc_weight=1.0):
     out = PDE_OUT_DIM[pde]
-    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     P = theta0.numel()
     inner, outer, final, aux, prm = make_maml_data(pde, n, n, T, K_steps, seed)
     g = torch.Generator().manual_seed(seed + 55)
     lrs = (1.0 + 0.3 * torch.randn(K_steps, P, generator=g)) if lr_tree else None
     cfg = dict(inner_steps=K_steps, inner_lr=inner_lr, inner_grad_clip=clip, softplus_lrs=True, outer_loss_decay=decay)
-    net = K.net_desc(L, W, out, OMEGA, True)
+    net = K.net_desc(L, W, out, OMEGA, True, nonlinearity=ACT)
     d = lambda sets: [_dev(K, s) for s in sets]
     got = K.maml_outer(net, pde, bc_weight, cfg, _dev(K, theta0), _dev(K, lrs) if lrs is not None else None,
                        [d(s) for s in inner], [d(s) for s in outer], d(final), d(aux), _dev(K, prm), T,
@@ -149,10 +171,10 @@ def check_maml(K, pde, W, L, n, T, K_steps=2, inner_lr=1e-3, clip=1e14, decay=0.
 
 def check_maml_adapt(K, pde, W, L, n, T, K_steps=3, inner_lr=1e-3, clip=1e14, seed=0):
     out = PDE_OUT_DIM[pde]
-    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     inner, _, final, _, prm = make_maml_data(pde, n, n, T, K_steps, seed)
     cfg = dict(inner_steps=K_steps, inner_lr=inner_lr, inner_grad_clip=clip, softplus_lrs=True, outer_loss_decay=0.0)
-    net = K.net_desc(L, W, out, OMEGA, True)
+    net = K.net_desc(L, W, out, OMEGA, True, nonlinearity=ACT)
     d = lambda sets: [_dev(K, s) for s in sets]
     thf, losses = K.maml_adapt(net, pde, 1.0, cfg, _dev(K, theta0), None, [d(s) for s in inner], d(final), _dev(K, prm), T)
     lf = oracle_loss_fn(pde, W, L, 1.0)
@@ -173,14 +195,14 @@ def check_maml_adapt(K, pde, W, L, n, T, K_steps=3, inner_lr=1e-3, clip=1e14, se
 
 def check_leap(K, pde, W, L, n, T, K_steps=3, inner_lr=1e-3, clip=1e14, inner_opt="adam", seed=0):
     out = PDE_OUT_DIM[pde]
-    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     sizes = synthetic.default_set_sizes(pde, n)
     loss0, prm = synthetic.make_tasks(pde, T, sizes, seed=seed + 1)
     step = [synthetic.make_tasks(pde, T, sizes, seed=seed + 20 + k)[0] for k in range(K_steps)]
     new = [synthetic.make_tasks(pde, T, sizes, seed=seed + 40 + k)[0] for k in range(K_steps)]
     cfg = dict(inner_steps=K_steps, inner_lr=inner_lr, inner_grad_clip=clip, norm=True, loss_in_distance=True,
                stabilize=True, inner_opt=inner_opt, beta1=0.9, beta2=0.99, eps=1e-8)
-    net = K.net_desc(L, W, out, OMEGA, True)
+    net = K.net_desc(L, W, out, OMEGA, True, nonlinearity=ACT)
     d = lambda sets: [_dev(K, s) for s in sets]
     got = K.leap_outer(net, pde, 1.0, cfg, _dev(K, theta0), d(loss0), [d(s) for s in step], [d(s) for s in new],
                        _dev(K, prm), T, want_theta_final=True)
@@ -205,15 +227,15 @@ def check_leap(K, pde, W, L, n, T, K_steps=3, inner_lr=1e-3, clip=1e14, inner_op
 
 
 def check_field_eval(K, W, L, out, n, T, seed=0):
-    theta = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     theta = torch.stack([theta * (1 + 0.05 * t) for t in range(T)])
     coords = torch.rand(T, n, 2, generator=torch.Generator().manual_seed(seed + 3)) * 2 - 1
-    net = K.net_desc(L, W, out, OMEGA, True)
+    net = K.net_desc(L, W, out, OMEGA, True, nonlinearity=ACT)
     u = K.field_eval(net, _dev(K, theta), _dev(K, coords), T)
     from oracle.field import nf_apply
     for t in range(T):
         params = unflatten_params(theta[t].double(), [W] * L, 2, out, True)
-        want = nf_apply(params, out, coords[t].double(), OMEGA)
+        want = nf_apply(params, out, coords[t].double(), OMEGA, ACT)
         e = rel_l2(u[t].cpu(), want)
         assert e < TOL, f"field_eval W={W} out={out}: {e}"
 
@@ -248,7 +270,7 @@ def check_maml_train_steps(K, pde, W, L, n, T, K_steps=2, steps=3, inner_lr=1e-2
                            grad_clip=1e14, inner_clip=1e14, optimizer="adam", seed=0, use_cuda_graph=False):
     from meta_pde_b200 import train
     out = PDE_OUT_DIM[pde]
-    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     P = theta0.numel()
     tr = train.MamlTrainer(pde, L, W, theta0, bsize=T, inner_steps=K_steps, inner_lr=inner_lr, outer_lr=outer_lr,
                            lr_inner_lr=lr_inner_lr, inner_grad_clip=inner_clip, grad_clip=grad_clip, optimizer=optimizer,
@@ -298,7 +320,7 @@ def check_maml_train_steps(K, pde, W, L, n, T, K_steps=2, steps=3, inner_lr=1e-2
 def check_leap_train_steps(K, pde, W, L, n, T, K_steps=3, steps=3, inner_lr=1e-3, outer_lr=1e-3, grad_clip=1e14, seed=0):
     from meta_pde_b200 import train
     out = PDE_OUT_DIM[pde]
-    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     tr = train.LeapTrainer(pde, L, W, theta0, bsize=T, inner_steps=K_steps, inner_lr=inner_lr, outer_lr=outer_lr,
                            grad_clip=grad_clip, kernels=K)
     lf = oracle_loss_fn(pde, W, L, 1.0)
@@ -329,7 +351,7 @@ def check_leap_train_steps(K, pde, W, L, n, T, K_steps=3, steps=3, inner_lr=1e-3
 def check_finetune_train_steps(K, pde, W, L, n, T, steps=3, outer_lr=1e-3, grad_clip=1e14, seed=0):
     from meta_pde_b200 import train
     out = PDE_OUT_DIM[pde]
-    theta0 = synthetic.siren_theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
+    theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
     tr = train.FinetuneTrainer(pde, L, W, theta0, bsize=T, outer_lr=outer_lr, grad_clip=grad_clip, kernels=K)
     lf = oracle_loss_fn(pde, W, L, 1.0)
     opt = ometa.FlaxAdam(outer_lr, 0.9, 0.99)
