@@ -267,7 +267,13 @@ def _check_state(name, got, want, got0, errs, bad):
 
 
 def check_maml_train_steps(K, pde, W, L, n, T, K_steps=2, steps=3, inner_lr=1e-2, outer_lr=1e-3, lr_inner_lr=0.5,
-                           grad_clip=1e14, inner_clip=1e14, optimizer="adam", seed=0, use_cuda_graph=False):
+                           grad_clip=1e14, inner_clip=1e14, optimizer="adam", seed=0, use_cuda_graph=False, resync=False):
+    """resync=False: trainer and oracle run free for `steps` steps from the same start.  resync=True: after every step the
+    oracle's state (theta, alpha tree, Adam moments) is set to the trainer's, so each step is compared from IDENTICAL
+    inputs.  Why both: the SIREN meta-gradient is ill-conditioned in theta (a 1.3e-6 relative difference in theta moves
+    ||g|| by 1.8e-4 at 3x64, omega 30), so a free-running float32 trajectory leaves the float64 one at ~10x per step
+    whatever the kernels do: measured on the emulator at 3x64 / 128 points / clip 1e-3, step 1 agrees to 4.6e-7, step 3 of
+    the free run to 1.8e-4 with glibc's 0.5-ulp sinf/cosf and to 1.8e-4 with compat.cuh's sincos alike."""
     from meta_pde_b200 import train
     out = PDE_OUT_DIM[pde]
     theta0 = _theta([W] * L, out, OMEGA, OMEGA, True, seed=seed, bias_scale=0.05)
@@ -313,6 +319,12 @@ def check_maml_train_steps(K, pde, W, L, n, T, K_steps=2, steps=3, inner_lr=1e-2
             _check_state("v_theta", tr.v_theta, st_theta["v"].detach(), None, errs, bad)
         _check_state("m_lrs", tr.m_lrs, st_lrs["m"].detach(), None, errs, bad)
         _check_state("v_lrs", tr.v_lrs, st_lrs["v"].detach(), None, errs, bad)
+        if resync:
+            f64 = lambda x, like: x.detach().cpu().double().reshape(like.shape)
+            o_theta, o_lrs = f64(tr.theta, o_theta), f64(tr.inner_lrs, o_lrs)
+            if opt_theta:
+                st_theta = dict(st_theta, m=f64(tr.m_theta, st_theta["m"]), v=f64(tr.v_theta, st_theta["v"]))
+            st_lrs = dict(st_lrs, m=f64(tr.m_lrs, st_lrs["m"]), v=f64(tr.v_lrs, st_lrs["v"]))
     assert not bad, f"MAML train_step {pde} {L}x{W} ({optimizer}, clip {grad_clip}): {bad} (all: {errs})"
     return errs, clipped
 
