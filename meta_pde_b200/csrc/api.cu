@@ -12,8 +12,31 @@
 #include <cstdlib>
 #include <mutex>
 #include <vector>
+#ifndef MPDE_EMU
+#include <nvtx3/nvToolsExt.h>
+#endif
 
 namespace mpde {
+
+// NVTX ranges around the entry points and every loss / grad / H.v evaluation inside the rollouts (SURVEY.md section 5:
+// the reference's own tracing is absl logging + TensorBoard scalars).  Off unless MPDE_NVTX=1 (read once per process):
+// with it, `ncu --nvtx --nvtx-include "mpde:maml_outer/"` profiles one rollout, and a timeline tool shows the
+// K forward evaluations and K reverse H.v evaluations of an outer step by name.  No NVTX call is made when it is off.
+#ifndef MPDE_EMU
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name) : on(enabled()) { if (on) nvtxRangePushA(name); }
+  ~NvtxRange() { if (on) nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+  static bool enabled() {
+    static const bool e = []() { const char* s = getenv("MPDE_NVTX"); return s && s[0] == '1'; }();
+    return e;
+  }
+};
+#else
+struct NvtxRange { explicit NvtxRange(const char*) {} };
+#endif
 
 std::atomic<long long> g_launches{0};
 
@@ -290,6 +313,7 @@ static int run_eval(const mpde_net_desc* net, const mpde_pde_desc* pde, int T, i
                     float* domain_residual, float* grad, float* hv, int want_grad, void* workspace, size_t ws_bytes,
                     void* stream) {
   if (!net || !pde || !theta || !points || !pde_params) return MPDE_INVALID_ARG;
+  NvtxRange nvtx(mode == MODE_LOSS ? "mpde:loss" : mode == MODE_GRAD ? "mpde:loss_grad" : "mpde:loss_hvp");
   if (mode == MODE_GRAD && !grad) return MPDE_INVALID_ARG;
   if (mode == MODE_HVP && (!hv || !v)) return MPDE_INVALID_ARG;
   EvalPlan pl;
@@ -568,6 +592,7 @@ size_t mpde_field_eval_workspace_bytes(const mpde_net_desc* net, int T) {
 
 int mpde_field_eval(const mpde_net_desc* net, int T, const float* theta, int64_t theta_task_stride, const float* coords,
                     int64_t coords_task_stride, int n, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  NvtxRange nvtx("mpde:field_eval");
   int rc = check_net(net, 0);
   if (rc) return rc;
   if (!theta || !coords || !out || T < 1 || n < 1) return MPDE_INVALID_ARG;
@@ -736,6 +761,7 @@ int mpde_outer_step(float* theta, int64_t n_theta, float* lrs, int64_t n_lrs, co
                     float* v_theta, float* m_lrs, float* v_lrs, int optimizer, int t_theta, float lr_theta, float b1,
                     float b2, float eps, int t_lrs, float lr_lrs, float b1_lrs, float b2_lrs, float eps_lrs, float clip,
                     float* sumsq_out, void* stream) {
+  NvtxRange nvtx("mpde:outer_step");
   if (!theta || !g_packed || n_theta < 1 || n_lrs < 0 || t_theta < 1) return MPDE_INVALID_ARG;
   if (optimizer != 0 && optimizer != 1) return MPDE_INVALID_ARG;
   if (optimizer == 1 && (!m_theta || !v_theta)) return MPDE_INVALID_ARG;
@@ -808,6 +834,7 @@ static int maml_impl(const mpde_net_desc* net, const mpde_pde_desc* pi, const mp
                      float* losses, float* meta_losses, float* aux_terms, float* theta_final, bool outer,
                      void* workspace, size_t workspace_bytes, void* stream) {
   MamlWs w;
+  NvtxRange nvtx(outer ? "mpde:maml_outer" : "mpde:maml_adapt");
   int rc = maml_ws(net, pi, po, cfg, T, outer, &w);
   if (rc) return rc;
   if (!theta0 || !inner_points || !final_points || !pde_params || !losses) return MPDE_INVALID_ARG;
@@ -950,6 +977,7 @@ int mpde_leap_outer(const mpde_net_desc* net, const mpde_pde_desc* pde, const mp
                     const mpde_points* new_points, const float* pde_params, float grad_scale, float* meta_grad,
                     float* losses, float* theta_final, void* workspace, size_t workspace_bytes, void* stream) {
   LeapWs w;
+  NvtxRange nvtx("mpde:leap_outer");
   int rc = leap_ws(net, pde, cfg, T, &w);
   if (rc) return rc;
   if (!theta0 || !loss0_points || !step_points || !new_points || !pde_params || !meta_grad || !losses) return MPDE_INVALID_ARG;
