@@ -101,7 +101,7 @@ def test_siren_init_and_param_tree():
     m = field.Model(Field, params)
     assert m.theta.numel() == 8580                                                     # P at 3x64
     with pytest.raises(NotImplementedError):
-        field.NeuralPotential.partial(sizes=[64], nonlinearity=None).spec()            # --nosiren: unsupported, no fallback
+        field.NeuralPotential.partial(sizes=[64], nonlinearity=None).spec()            # neither np.sin nor nn.swish: no fallback
 
 
 def test_checkpoint_layout_roundtrip(tmp_path):

@@ -53,7 +53,62 @@ def test_compat_field_accepts_swish():
         field.NeuralPotential.partial(sizes=[64], nonlinearity=field.swish, n_fourier=4).spec()
 
 
+def _compat_swish_loss_vs_oracle(K, device):
+    """The plugin surface with --nosiren: pde.BaseField.partial(nonlinearity=field.swish) -> Model -> pde.loss_fn (one fused
+    launch, autograd to first order through mpde_loss_grad) and field_fn(x), against the float64 oracle."""
+    from helpers import rel_l2
+    from meta_pde_b200.compat import flags as cflags
+    cflags.define_maml()             # idempotent: the other compat test modules do the same at import
+    cflags.ensure_parsed(["test"])
+    from meta_pde_b200.compat import field, pdes, random as jr
+    from meta_pde_b200.compat.flags import FLAGS
+    from oracle import meta as ometa
+    from oracle.field import nf_apply, unflatten_params
+    import helpers
+    saved = (FLAGS.bc_weight, FLAGS.xmin)
+    FLAGS.bc_weight, FLAGS.xmin = 1.0, -1.0
+    try:
+        pde = pdes.get_pde("poisson")
+        Field = pde.BaseField.partial(sizes=[32, 32], dense_args=(), nonlinearity=field.swish, omega=1.0, omega0=3.0, log_scale=True)
+        _, params = Field.init_by_shape(jr.PRNGKey(5), [((1, 2), "float32")])
+        model = field.Model(Field, params)
+        assert model.net_desc(K).nonlinearity == 1
+        prm = pde.sample_params(jr.PRNGKey(1))
+        pts = pde.sample_points(jr.PRNGKey(2), 64, prm)
+        theta = model.theta.clone().requires_grad_(True)
+        b, d = pde.loss_fn(field.Model(model.module, theta), pts, prm)
+        loss = torch.stack(list(b.values())).sum() + torch.stack(list(d.values())).sum()
+        (g,) = torch.autograd.grad(loss, theta)
+        sets = [torch.as_tensor(s, dtype=torch.float32).cpu().reshape(1, -1, 2) for s in pde.abi_sets(pts)]   # oracle side: CPU
+        abi_prm = pde.abi_params(prm).reshape(1, -1).cpu()
+        lf = ometa.make_loss_fn("poisson", ometa.NetCfg([32, 32], 1.0, True, 1, "swish"), 1.0)
+        th64 = model.theta.detach().cpu().double().requires_grad_(True)
+        l64, _ = lf(th64, helpers.oracle_points("poisson", sets, 0), helpers.oracle_params("poisson", abi_prm, 0))
+        (g64,) = torch.autograd.grad(l64, th64)
+        assert rel_l2(loss.detach().cpu(), l64.detach()) < 1e-4 and rel_l2(g.detach().cpu(), g64) < 1e-4
+        x = torch.as_tensor(pts[-1], dtype=torch.float32).cpu().reshape(-1, 2)
+        u = model(x.to(device))
+        want = nf_apply(unflatten_params(th64.detach(), [32, 32], 2, 1, True), 1, x.double(), 1.0, "swish").sum(-1)
+        assert rel_l2(u.cpu(), want) < 1e-4
+    finally:
+        FLAGS.bc_weight, FLAGS.xmin = saved
+
+
+def test_emu_compat_surface_with_swish(emu_kernels, monkeypatch):
+    if torch.cuda.is_available():
+        pytest.skip("compat models live on the CUDA device when there is one; the GPU twin below covers it")
+    from meta_pde_b200 import ops
+    monkeypatch.setattr(ops, "kernels", lambda device=None: emu_kernels)     # TEST ONLY: host logic over the emulator build
+    _compat_swish_loss_vs_oracle(emu_kernels, "cpu")
+
+
 # ------------------------------------------------------------------------------------------- CUDA library
+@pytest.mark.gpu
+def test_gpu_compat_surface_with_swish(gpu_kernels):
+    _compat_swish_loss_vs_oracle(gpu_kernels, "cuda")
+
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("pde,W,L,n", [
     ("poisson", 64, 3, 1024),            # the README command's shape with --nosiren
